@@ -1,0 +1,172 @@
+/*
+ * katib_b200.h -- C ABI of libkatib_b200.so: the B200 (sm_100a) arithmetic behind Katib's
+ * goptuna suggestion service (TPE, CMA-ES, Sobol).
+ *
+ * The reference has no C FFI on this path: pkg/suggestion/v1beta1/goptuna is pure Go built with
+ * CGO_ENABLED=0 (cmd/suggestion/goptuna/v1beta1/Dockerfile:18) and calls the Go module
+ * github.com/c-bata/goptuna v0.8.0 (go.mod:8).  Each entry point below names the goptuna call the
+ * reference makes at that spot (reference file:line = the call site a cgo shim would replace);
+ * INTEGRATION.md shows the cgo stub.
+ *
+ * Conventions
+ *   - every function returns 0 (KB_OK) or a negative kb_status; kb_last_error(ctx) gives the text,
+ *     valid until the next call on that ctx (ctx == NULL: the creating thread's last kb_create error)
+ *   - one kb_ctx per GPU per process (one process per GPU when sharding); calls on one ctx are
+ *     serialised by an internal mutex; the library never keeps a caller pointer after returning
+ *   - "internal representation" = goptuna's: one float64 per parameter; categorical = index into
+ *     Choices, int = float64(int)   (converter.go:277-343)
+ *   - host pointers unless the name ends in _device; *_device entry points take device pointers in
+ *     the ctx's GPU memory and a cudaStream_t passed as void* (NULL = the ctx's own stream)
+ *   - there is no CPU fallback: without a usable sm_100 device kb_create fails
+ */
+#ifndef KATIB_B200_H
+#define KATIB_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kb_ctx kb_ctx;
+
+typedef enum {
+    KB_OK = 0,
+    KB_ERR_INVALID = -1,     /* bad argument */
+    KB_ERR_CUDA = -2,        /* CUDA runtime / launch failure */
+    KB_ERR_STATE = -3,       /* call order (e.g. scoring before a history was set) */
+    KB_ERR_COMM = -4,        /* NCCL missing or failed */
+    KB_ERR_UNSUPPORTED = -5, /* size beyond a stated limit */
+    KB_ERR_OVERFLOW = -6     /* internal near-tie table overflowed (see kb_tpe_score_select) */
+} kb_status;
+
+/* Parameter kinds = the goptuna distribution types toGoptunaSearchSpace emits (converter.go:110-184) */
+typedef enum {
+    KB_UNIFORM = 0,     /* goptuna.UniformDistribution{Low,High}             DOUBLE, no step */
+    KB_DISCRETE = 1,    /* goptuna.DiscreteUniformDistribution{Low,High,Q}   DOUBLE with step */
+    KB_INT = 2,         /* goptuna.IntUniformDistribution{Low,High}          INT, no step */
+    KB_STEP_INT = 3,    /* goptuna.StepIntUniformDistribution{Low,High,Step} INT with step */
+    KB_CATEGORICAL = 4  /* goptuna.CategoricalDistribution{Choices}          CATEGORICAL and DISCRETE */
+} kb_kind;
+
+#define KB_MAX_PARAMS 1024
+#define KB_MAX_CHOICES 4096
+#define KB_SOBOL_MAX_DIM 1024
+
+int kb_version(void);
+const char *kb_last_error(const kb_ctx *ctx);
+
+/* One context on CUDA device `device`.  Replaces goptuna.CreateStudy (converter.go:369): the ctx is
+ * the per-experiment state (search space, history, optimiser state) held in HBM. */
+int kb_create(int device, kb_ctx **out);
+int kb_destroy(kb_ctx *ctx);
+/* out[0]=SM count, out[1]=cc major, out[2]=cc minor, out[3]=SM clock kHz, out[4]=L2 bytes */
+int kb_device_info(const kb_ctx *ctx, int64_t out[5]);
+/* the ctx's own stream as a cudaStream_t (for event timing on the launching stream) */
+void *kb_stream(const kb_ctx *ctx);
+
+/* ---- multi-GPU: one process per GPU, NCCL over NVLink --------------------------------------- */
+/* 128-byte NCCL unique id made on rank 0 and handed to every rank by the host plumbing. */
+int kb_comm_unique_id(void *out128);
+int kb_comm_init(kb_ctx *ctx, int world, int rank, const void *unique_id128);
+int kb_comm_world(const kb_ctx *ctx, int *world, int *rank);
+
+/* ---- search space ---------------------------------------------------------------------------
+ * Replaces goptuna.StudyOptionDefineSearchSpace(searchSpace) (converter.go:360); the arrays are
+ * toGoptunaSearchSpace's output (converter.go:110-184) in a fixed parameter order chosen by the
+ * caller.  step[] is Q / Step (ignored for UNIFORM, INT, CATEGORICAL); n_choices[] only for
+ * CATEGORICAL.  low/high for INT kinds are the integer bounds as doubles. */
+int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, const double *low,
+                 const double *high, const double *step, const int32_t *n_choices);
+
+/* ---- TPE ------------------------------------------------------------------------------------
+ * kb_tpe_set_history replaces the per-parameter history walk of tpe.Sampler.Sample
+ * (getObservationPairs over study.GetTrials(); reached from sample.go:48-90): Complete trials only
+ * (service.go:134-137), values[n_trials x n_params] row-major internal representation,
+ * loss[n_trials] = objective already sign-flipped so that lower is better
+ * (toGoptunaDirection, converter.go:31-36).  It uploads the history and builds, on the GPU, the
+ * below/above split and both Parzen estimators of every parameter. */
+int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss);
+
+/* Estimator of parameter `param`, side 0 = below (l), 1 = above (g): K entries sorted by mu.
+ * Buffers hold `cap` doubles; *K is set even when cap is too small (then KB_ERR_INVALID).
+ * For CATEGORICAL parameters mu/sigma are NULL-able and w receives the n_choices probabilities. */
+int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, double *w, double *mu,
+                      double *sigma, int cap, double *p_accept);
+
+/* Score every candidate: scores[i*n_params + d] = log l(x) - log g(x) (FP32 arithmetic, FP64
+ * accumulation) -- tpe.Sampler.gmmLogPDF / categoricalLogPDF on a caller-supplied
+ * candidate set.  cand[n_cand x n_params] row-major, in the sampler's working domain: UNIFORM /
+ * INT / STEP_INT as is, DISCRETE shifted by -low (goptuna shifts to [0, high-low]), CATEGORICAL
+ * the choice index. */
+int kb_tpe_scores(kb_ctx *ctx, int64_t n_cand, const double *cand, double *scores);
+
+/* tpe.Sampler.compare on a caller-supplied candidate set, per parameter: index of the winning
+ * candidate (first maximum), the value Sampler.Sample would return for it (DISCRETE: shifted back
+ * and clamped), and its FP64 score.  index_offset is added to reported indices (this rank's first
+ * global candidate index when the set is sharded).  With a communicator set (kb_comm_init) every
+ * rank passes its own slice and all ranks receive the global winners (one NCCL collective).
+ * Winners are decided in FP64: the FP32 pass keeps every distinct value within a margin of the
+ * running maximum and those are re-scored in FP64.  KB_ERR_OVERFLOW if that table fills. */
+int kb_tpe_score_select(kb_ctx *ctx, int64_t n_cand, const double *cand, int64_t index_offset,
+                        int64_t *out_index, double *out_value, double *out_score);
+/* Same with candidates already in HBM (device pointer, same layout). */
+int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const double *cand_device,
+                               int64_t index_offset, int64_t *out_index, double *out_value,
+                               double *out_score, void *stream);
+
+/* Full tpe.Sampler.Sample for every parameter (sample.go:48-90): draw n_ei_candidates from l(x)
+ * on the device (Philox4x32-10 keyed by seed; goptuna's math/rand stream is not reproducible),
+ * score, select.  out_value[n_params] in internal representation. */
+int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t seed, double *out_value);
+/* Draw only (sampleFromGMM / sampleFromCategoricalDist): cand[n x n_params] row-major, working
+ * domain.  cand_device may be NULL when cand_host is given and vice versa. */
+int kb_tpe_sample_candidates(kb_ctx *ctx, int64_t n, uint64_t seed, double *cand_host,
+                             double *cand_device, void *stream);
+
+/* ---- Sobol ----------------------------------------------------------------------------------
+ * sobol.Engine.Draw() n_points times starting at sequence index first_index (sobol.NewSampler,
+ * converter.go:94; reached through trial.CallRelativeSampler, sample.go:39).  Joe-Kuo direction
+ * numbers, 32 bits, gray-code order, point 0 = origin.  out[p*dim + d] = u in [0,1); with low/high
+ * non-NULL, low[d] + u*(high[d]-low[d]) with separately rounded multiply and add (Go does not fuse). */
+int kb_sobol_fill(kb_ctx *ctx, int dim, uint64_t first_index, int64_t n_points, const double *low,
+                  const double *high, double *out);
+int kb_sobol_fill_device(kb_ctx *ctx, int dim, uint64_t first_index, int64_t n_points,
+                         const double *low, const double *high, double *out_device, void *stream);
+
+/* ---- CMA-ES ---------------------------------------------------------------------------------
+ * cmaes.NewOptimizer(mean, sigma, OptimizerOptionBounds, [popsize]) -- created by
+ * cmaes.Sampler.SampleRelative (converter.go:41-68, sample.go:39).  popsize 0 = 4+floor(3 ln n).
+ * lo/hi NULL = unbounded. One optimiser per ctx. */
+int kb_cmaes_create(kb_ctx *ctx, int n, const double *mean, double sigma, int popsize,
+                    const double *lo, const double *hi);
+/* Optimizer.Ask() lam times in one batch: x[k*n+i] = m_i + sigma*(B diag(D) z_k)_i.  z[lam x n]
+ * row-major supplied by the caller (NULL: drawn on the device, Philox keyed by seed).  No
+ * resampling; out-of-bounds coordinates are clipped when bounds exist (repairInfeasibleParams). */
+int kb_cmaes_ask(kb_ctx *ctx, int lam, const double *z, uint64_t seed, double *x);
+/* Optimizer.Tell(solutions): x[popsize x n] row-major, f[popsize] lower is better. */
+int kb_cmaes_tell(kb_ctx *ctx, const double *x, const double *f);
+/* Any pointer may be NULL.  B[i*n+j] = component i of eigenvector j, D = sqrt(eigenvalues), both
+ * canonical (ascending, largest-|component| positive); they refer to the current C. */
+int kb_cmaes_get_state(kb_ctx *ctx, double *mean, double *sigma, double *C, double *p_sigma,
+                       double *p_c, double *B, double *D, int *generation);
+/* Override the cached factors (parity hook: feed another solver's B, D). */
+int kb_cmaes_set_eig(kb_ctx *ctx, const double *B, const double *D);
+/* Symmetric eigendecomposition (parallel cyclic Jacobi, FP64) standing in for gonum mat.EigenSym:
+ * A[n x n] row-major -> w ascending, V[i*n+j] = component i of eigenvector j. */
+int kb_eigh(kb_ctx *ctx, int n, const double *A, double *w, double *V);
+
+/* ---- random -----------------------------------------------------------------------------------
+ * goptuna.RandomSampler (converter.go:96-106): out[i*n_params + d] uniform over each parameter's
+ * distribution, internal representation, Philox keyed by (seed, first_index + i). */
+int kb_random_fill(kb_ctx *ctx, uint64_t seed, uint64_t first_index, int64_t n, double *out);
+
+/* ---- measurement helpers (used by bench.py and the profiles) ----------------------------------
+ * which: 0 = MUFU.EX2 Gop/s, 1 = FP32 FFMA GFMA/s, 2 = FP64 DFMA GFMA/s, 3 = HBM write GB/s,
+ * 4 = HBM copy GB/s.  Runs a saturating micro-kernel on the ctx's device and returns the rate. */
+int kb_peak_measure(kb_ctx *ctx, int which, double *out);
+/* number of kernels this library has launched on this ctx since creation */
+int64_t kb_launch_count(const kb_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,167 @@
+// kb_internal.cuh -- shared state and helpers of libkatib_b200.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/katib_b200.h"
+
+// ---- per-parameter descriptor, resident in HBM (kb_ctx::d_dims) -----------------------------------
+// Working domain of goptuna's sampleNumerical for the parameter: [lo, hi], quantum q (0 = continuous),
+// shift = amount subtracted from stored history values (DISCRETE only).
+struct KbDim {
+    int32_t kind;
+    int32_t n_choices;
+    double lo, hi, q, shift;  // sampling range of sampleNumerical
+    double ext_lo, ext_hi;    // distribution bounds (for the final clamp of DISCRETE)
+    // Parzen tables (FP64, parity + FP64 re-scoring); capacity kcap entries per side
+    int32_t K[2];             // components per side (n_side + 1)
+    int32_t Kpad[2];          // padded to KB_TABLE_PAD
+    double *mu[2], *sigma[2], *w[2], *logc[2];  // logc = log(w / (sqrt(2pi) sigma p_accept))
+    double p_accept[2];
+    double L[2];              // max_j logc (fixed log-sum-exp shift)
+    // FP32 folded tables for the scoring kernels: float4 per component, Kpad entries
+    //   continuous: {mu_hi, c', m' = -mu_lo*c', k'}     c' = sqrt(log2e/2)/sigma_n, k' = (logc-L)*log2e
+    //   quantised : {mu_hi, r,  m_r = -mu_lo*r,  w }     r  = 1/(sqrt2 sigma_n)
+    float4 *tab[2];
+    // categorical: probabilities and the log-ratio table
+    double *cat_p[2];
+    double *cat_score;        // log pl[c] - log pg[c]
+    int32_t *cat_rank;        // dense rank of cat_score (ties share a rank)
+    int32_t numeric_slot;     // index among numeric dims (-1 for categorical)
+};
+
+#define KB_TABLE_PAD 32
+
+// near-tie table (per numeric parameter): open-addressing set keyed by the candidate's f64 bits
+struct KbTie {
+    unsigned long long key;     // f64 bits of the candidate value, ~0 = empty
+    unsigned long long minidx;  // lowest global index seen with that value
+};
+#define KB_TIE_SLOTS (1u << 16)
+#define KB_TIE_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+struct KbSelect {                // per-parameter running selection state (device)
+    unsigned int gmax_bits;      // orderable bits of the running FP32 maximum
+    unsigned int overflow;
+    unsigned int tie_count;
+    unsigned int pad;
+    unsigned long long cat_best; // categorical: (rank << 32) | ~idx32
+};
+
+struct KbWinner {                // per-parameter result (device + host mirror)
+    double score;
+    long long index;
+    double value;
+};
+
+struct KbComm;  // kb_comm.cu
+struct KbCma;   // kb_cmaes.cu
+
+struct kb_ctx {
+    int device = 0;
+    cudaDeviceProp prop{};
+    cudaStream_t stream = nullptr;   // compute
+    cudaStream_t copy_stream = nullptr;
+    std::mutex mu;
+    mutable std::string err;
+    int64_t launches = 0;
+
+    // search space
+    int D = 0;
+    std::vector<KbDim> h_dims;
+    KbDim *d_dims = nullptr;
+    int n_numeric = 0, n_cont = 0, n_quant = 0, n_cat = 0;
+    std::vector<int> cont_dims, quant_dims, cat_dims;
+    int *d_cont_dims = nullptr, *d_quant_dims = nullptr, *d_cat_dims = nullptr;
+
+    // history
+    int64_t n_trials = 0;
+    double *d_values = nullptr, *d_loss = nullptr;
+    int64_t hist_cap = 0;
+    int n_below = 0;
+    int32_t *d_pos = nullptr;        // [2][n]: position of trial i inside below / above, or -1
+    double *d_sort_keys = nullptr;   // scratch for the bitonic sorts
+    uint32_t *d_sort_idx = nullptr;
+    int64_t sort_cap = 0;
+    double *d_tabmem = nullptr;      // arena behind the KbDim table pointers
+    size_t tabmem_bytes = 0;
+    bool history_ready = false;
+
+    // scoring scratch
+    int64_t chunk_cap = 0;           // candidates per staged chunk
+    double *d_cand_chunk[2] = {nullptr, nullptr};   // H2D landing buffers (row-major f64)
+    float2 *d_stage_cont = nullptr;  // [n_cont][chunk]   (x_hi, x_lo) normalised
+    float4 *d_stage_quant = nullptr; // [n_quant][chunk]  (lb_hi, lb_lo, ub_hi, ub_lo) normalised
+    double *d_scores_chunk = nullptr; // [chunk x D] dense scores (kb_tpe_scores only)
+    KbSelect *d_sel = nullptr;       // [D]
+    KbTie *d_tie = nullptr;          // [n_numeric][KB_TIE_SLOTS]
+    KbWinner *d_win = nullptr;       // [D]
+    KbWinner *d_win_all = nullptr;   // [world][D] (gather target)
+    float *d_tie_score = nullptr;    // [n_numeric][KB_TIE_SLOTS] FP32 score stored with each near-tie entry
+    void *d_partial = nullptr;       // [n_numeric][RS_BLOCKS] partial FP64 winners (kb_tpe_score.cu)
+    int *d_slot_of_dim = nullptr;    // [D] index of a parameter inside its cont / quant / cat list
+    int *d_numeric_dims = nullptr;   // [n_numeric] parameter index per numeric slot
+    KbWinner *h_win = nullptr;       // pinned host mirror of d_win
+    cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+
+    uint32_t *d_sobol_v = nullptr;   // [32][KB_SOBOL_MAX_DIM] direction numbers, bit-major
+
+    KbComm *comm = nullptr;
+    KbCma *cma = nullptr;
+};
+
+// ---- error plumbing ---------------------------------------------------------------------------------
+int kb_fail(const kb_ctx *ctx, int code, const char *fmt, ...);
+#define KB_CUDA(ctx, call)                                                                         \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return kb_fail(ctx, KB_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call,          \
+                           cudaGetErrorString(e__));                                               \
+    } while (0)
+#define KB_LAUNCH_CHECK(ctx)                                                                       \
+    do {                                                                                           \
+        (ctx)->launches++;                                                                         \
+        KB_CUDA(ctx, cudaGetLastError());                                                          \
+    } while (0)
+
+struct KbDeviceGuard {
+    int prev = -1;
+    explicit KbDeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~KbDeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// cross-file entry points
+int kb_tpe_free(kb_ctx *ctx);
+int kb_sobol_free(kb_ctx *ctx);
+int kb_cmaes_free(kb_ctx *ctx);
+int kb_comm_free(kb_ctx *ctx);
+int kb_comm_allgather(kb_ctx *ctx, const void *send, void *recv, size_t bytes, cudaStream_t s);
+
+// ---- device helpers ------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned int kb_f32_orderable(float f) {
+    unsigned int b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float kb_f32_from_orderable(unsigned int u) {
+    unsigned int b = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
+    return __uint_as_float(b);
+}
+__device__ __forceinline__ float kb_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float kb_lg2(float x) {
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+#endif

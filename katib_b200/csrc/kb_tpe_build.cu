@@ -1,0 +1,413 @@
+// kb_tpe_build.cu -- history upload, below/above split and Parzen-estimator construction on the GPU.
+//
+// Replaces, per parameter, what goptuna's tpe.Sampler.Sample does before it draws candidates
+// (module not in the reference tree, go.mod:8; reached from sample.go:48-90 through trial.Suggest*):
+//   getObservationPairs      -> the dense values[n x D] / loss[n] arrays handed to kb_tpe_set_history
+//   splitObservationPairs    -> split_kernel (stable order by loss, gamma(n) = min(ceil(0.1 n), 25))
+//   NewParzenEstimator       -> parzen_kernel (sort, prior insert, neighbour sigmas, magic clip, weight ramp)
+//   sampleCategorical tables -> categorical_kernel
+// Everything here is FP64 with the operation order of the CPU oracle (oracle/tpe.c); the file is
+// compiled with -fmad=false so that mu, sigma and the weights come out bit-identical to it.
+// The FP32 "folded" tables consumed by the scoring kernels are derived at the end of parzen_kernel.
+#include <math.h>
+
+#include "kb_internal.cuh"
+
+#define BUILD_THREADS 1024
+#define KB_EPS 1e-12
+
+static int next_pow2(int64_t v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+static inline int pad_to(int v, int m) { return (v + m - 1) / m * m; }
+
+// ---- bitonic sort of (key, idx) pairs by (key asc, idx asc), one CTA, arrays in global memory -------------
+__device__ void bitonic_sort_pairs(double *keys, uint32_t *idx, int npad) {
+    for (int k = 2; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+                int ixj = i ^ j;
+                if (ixj > i) {
+                    double a = keys[i], b = keys[ixj];
+                    uint32_t ia = idx[i], ib = idx[ixj];
+                    bool gt = (a > b) || (a == b && ia > ib);
+                    bool up = (i & k) == 0;
+                    if (gt == up) { keys[i] = b; keys[ixj] = a; idx[i] = ib; idx[ixj] = ia; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__device__ __forceinline__ int tpe_gamma_dev(int n) {
+    int a = (int)ceil(0.1 * (double)n);
+    return a > 25 ? 25 : a;
+}
+
+// weight of the observation at position `pos` (trial order) among m observations: tpe.DefaultWeights
+__device__ __forceinline__ double tpe_ramp(int pos, int m) {
+    if (m < 25) return 1.0;
+    int r = m - 25;
+    if (pos >= r) return 1.0;
+    double start = 1.0 / (double)m;
+    if (r == 1) return start;
+    double step = (1.0 - start) / (double)(r - 1);
+    return start + (double)pos * step;  // -fmad=false: separately rounded, like Go
+}
+
+// ---- split: rank trials by loss; pos[0][i] / pos[1][i] = position of trial i inside below / above --------
+__global__ void __launch_bounds__(BUILD_THREADS)
+split_kernel(const double *__restrict__ loss, int n, int npad, double *keys, uint32_t *idx, int32_t *pos) {
+    __shared__ int s_cnt[BUILD_THREADS];
+    for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+        keys[i] = i < n ? loss[i] : INFINITY;
+        idx[i] = i < n ? (uint32_t)i : 0xFFFFFFFFu;
+    }
+    __syncthreads();
+    bitonic_sort_pairs(keys, idx, npad);
+    const int nb = tpe_gamma_dev(n);
+    // flag: pos[0][trial] = 1 if the trial is among the nb best
+    for (int i = threadIdx.x; i < n; i += blockDim.x) pos[i] = 0;
+    __syncthreads();
+    for (int r = threadIdx.x; r < nb; r += blockDim.x) pos[idx[r]] = 1;
+    __syncthreads();
+    // positions in trial order: exclusive scan of the flags (segment per thread + scan of segment counts)
+    const int seg = (n + blockDim.x - 1) / blockDim.x;
+    const int b0 = threadIdx.x * seg, b1 = min(n, b0 + seg);
+    int c = 0;
+    for (int i = b0; i < b1; i++) c += pos[i];
+    s_cnt[threadIdx.x] = c;
+    __syncthreads();
+    for (int off = 1; off < blockDim.x; off <<= 1) {
+        int v = threadIdx.x >= off ? s_cnt[threadIdx.x - off] : 0;
+        __syncthreads();
+        s_cnt[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int below_before = s_cnt[threadIdx.x] - c;
+    for (int i = b0; i < b1; i++) {
+        int f = pos[i];
+        int above_before = i - below_before;
+        pos[i] = f ? below_before : -1;
+        pos[n + i] = f ? -1 : above_before;
+        below_before += f;
+    }
+}
+
+// ---- Parzen estimator of one (numeric parameter, side) ---------------------------------------------------
+__global__ void __launch_bounds__(BUILD_THREADS)
+parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ values, int n, int D, int nb,
+              const int32_t *__restrict__ pos, int npad, double *keys_all, uint32_t *idx_all) {
+    __shared__ double s_red[BUILD_THREADS];
+    __shared__ double s_scalar[2];
+    __shared__ int s_int[BUILD_THREADS];
+    const int slot = blockIdx.x, side = blockIdx.y;
+    const int d = numeric_dims[slot];
+    KbDim &dm = dims[d];
+    const int m = side == 0 ? nb : n - nb;  // observations on this side
+    const int K = m + 1;
+    double *keys = keys_all + ((size_t)slot * 2 + side) * npad;
+    uint32_t *idx = idx_all + ((size_t)slot * 2 + side) * npad;
+    const double low = dm.lo, high = dm.hi, shift = dm.shift;
+    double *mu = dm.mu[side], *sg = dm.sigma[side], *w = dm.w[side], *logc = dm.logc[side];
+    const int tid = threadIdx.x, nt = blockDim.x;
+
+    for (int i = tid; i < npad; i += nt) { keys[i] = INFINITY; idx[i] = 0xFFFFFFFFu; }
+    __syncthreads();
+    for (int i = tid; i < n; i += nt) {
+        int p = pos[side * n + i];
+        if (p >= 0) { keys[p] = values[(size_t)i * D + d] - shift; idx[p] = (uint32_t)p; }
+    }
+    __syncthreads();
+    bitonic_sort_pairs(keys, idx, npad);
+
+    const double prior_mu = 0.5 * (low + high), prior_sigma = 1.0 * (high - low);
+    // prior_pos = number of observations strictly below prior_mu (searchsorted, side='left')
+    int cnt = 0;
+    for (int i = tid; i < m; i += nt) cnt += keys[i] < prior_mu ? 1 : 0;
+    s_int[tid] = cnt;
+    __syncthreads();
+    for (int off = nt >> 1; off > 0; off >>= 1) {
+        if (tid < off) s_int[tid] += s_int[tid + off];
+        __syncthreads();
+    }
+    const int prior_pos = s_int[0];
+    __syncthreads();
+
+    for (int j = tid; j < K; j += nt) {
+        if (j == prior_pos) { mu[j] = prior_mu; w[j] = 1.0 /* prior_weight */; }
+        else {
+            int s = j < prior_pos ? j : j - 1;
+            mu[j] = keys[s];
+            w[j] = tpe_ramp((int)idx[s], m);
+        }
+    }
+    __syncthreads();
+    if (m == 0) {
+        if (tid == 0) sg[0] = prior_sigma;
+    } else {
+        for (int j = tid; j < K; j += nt) {
+            double left = j == 0 ? low : mu[j - 1];
+            double right = j == K - 1 ? high : mu[j + 1];
+            double a = mu[j] - left, b = right - mu[j];
+            double s = a > b ? a : b;
+            if (j == 0) s = mu[1] - mu[0];              // consider_endpoints = false
+            if (j == K - 1) s = mu[K - 1] - mu[K - 2];
+            sg[j] = s;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {  // sequential sum: the oracle's (and a Go for-loop's) rounding order
+        double s = 0.0;
+        for (int j = 0; j < K; j++) s += w[j];
+        s_scalar[0] = s;
+    }
+    __syncthreads();
+    {
+        const double wsum = s_scalar[0];
+        const double maxsigma = 1.0 * (high - low);
+        double dd = 1.0 + (double)K;
+        if (dd > 100.0) dd = 100.0;
+        const double minsigma = 1.0 * (high - low) / dd;  // consider_magic_clip = true
+        for (int j = tid; j < K; j += nt) {
+            w[j] = w[j] / wsum;
+            double s = sg[j];
+            if (s < minsigma) s = minsigma;
+            if (s > maxsigma) s = maxsigma;
+            if (j == prior_pos) s = prior_sigma;
+            sg[j] = s;
+        }
+    }
+    __syncthreads();
+    // p_accept = sum_j w_j (Phi(high) - Phi(low)); terms in parallel, summed in order by one thread
+    for (int j = tid; j < K; j += nt) {
+        double den = sqrt(2.0) * sg[j];
+        if (den < KB_EPS) den = KB_EPS;
+        double ch = 0.5 * (1.0 + erf((high - mu[j]) / den));
+        double cl = 0.5 * (1.0 + erf((low - mu[j]) / den));
+        keys[j] = w[j] * (ch - cl);  // keys[] is free again (npad >= K)
+    }
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0.0;
+        for (int j = 0; j < K; j++) s += keys[j];
+        s_scalar[1] = s;
+    }
+    __syncthreads();
+    const double p_accept = s_scalar[1];
+    double lmax = -INFINITY;
+    for (int j = tid; j < K; j += nt) {
+        double Z = sqrt(2.0 * M_PI) * sg[j];
+        double lc = log(w[j] / Z / p_accept);
+        logc[j] = lc;
+        lmax = fmax(lmax, lc);
+    }
+    s_red[tid] = lmax;
+    __syncthreads();
+    for (int off = nt >> 1; off > 0; off >>= 1) {
+        if (tid < off) s_red[tid] = fmax(s_red[tid], s_red[tid + off]);
+        __syncthreads();
+    }
+    const double L = s_red[0];
+    const int Kpad = (K + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
+    if (tid == 0) { dm.K[side] = K; dm.Kpad[side] = Kpad; dm.p_accept[side] = p_accept; dm.L[side] = L; }
+    // FP32 folded tables in normalised coordinates x_n = (x - low) / (high - low)
+    const double inv_range = 1.0 / (high - low);
+    const double LOG2E = 1.4426950408889634;
+    float4 *tab = dm.tab[side];
+    const bool quant = dm.q > 0.0;
+    for (int j = tid; j < Kpad; j += nt) {
+        float4 e;
+        if (j >= K) {
+            e = quant ? make_float4(0.f, 0.f, 0.f, 0.f) : make_float4(0.f, 0.f, 0.f, -INFINITY);
+        } else {
+            double mun = (mu[j] - low) * inv_range;
+            float mh = (float)mun;
+            double ml = mun - (double)mh;
+            if (quant) {
+                double den = sqrt(2.0) * sg[j];
+                if (den < KB_EPS) den = KB_EPS;
+                float r = (float)((high - low) / den);  // 1 / (sqrt2 sigma_n)
+                e = make_float4(mh, r, (float)(-ml * (double)r), (float)w[j]);
+            } else {
+                double s = sg[j] > KB_EPS ? sg[j] : KB_EPS;
+                float c = (float)(sqrt(0.5 * LOG2E) * (high - low) / s);
+                e = make_float4(mh, c, (float)(-ml * (double)c), (float)((logc[j] - L) * LOG2E));
+            }
+        }
+        tab[j] = e;
+    }
+}
+
+// ---- categorical parameters: weighted bincount (trial order) + prior weight, log ratio, ranks ------------
+__global__ void categorical_kernel(KbDim *dims, const int *cat_dims, const double *__restrict__ values, int n, int D,
+                                   int nb, const int32_t *__restrict__ pos) {
+    __shared__ double s_sum[2];
+    const int d = cat_dims[blockIdx.x];
+    KbDim &dm = dims[d];
+    const int C = dm.n_choices;
+    for (int side = 0; side < 2; side++) {
+        const int m = side == 0 ? nb : n - nb;
+        double *p = dm.cat_p[side];
+        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+            double acc = 0.0;
+            for (int i = 0; i < n; i++) {
+                int ps = pos[side * n + i];
+                if (ps >= 0 && (int)values[(size_t)i * D + d] == c) acc += tpe_ramp(ps, m);
+            }
+            p[c] = acc + 1.0;  // prior_weight
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double s = 0.0;
+            for (int c = 0; c < C; c++) s += p[c];
+            s_sum[side] = s;
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += blockDim.x) p[c] = p[c] / s_sum[side];
+        __syncthreads();
+    }
+    for (int c = threadIdx.x; c < C; c += blockDim.x) dm.cat_score[c] = log(dm.cat_p[0][c]) - log(dm.cat_p[1][c]);
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {  // rank = number of strictly smaller scores (ties share it)
+        double sc = dm.cat_score[c];
+        int r = 0;
+        for (int e = 0; e < C; e++) r += dm.cat_score[e] < sc ? 1 : 0;
+        dm.cat_rank[c] = r;
+    }
+    if (threadIdx.x == 0) { dm.K[0] = dm.K[1] = C; dm.Kpad[0] = dm.Kpad[1] = C; }
+}
+
+// ---- host side -----------------------------------------------------------------------------------------------
+int kb_tpe_free_history(kb_ctx *ctx) {
+    cudaFree(ctx->d_values); cudaFree(ctx->d_loss); cudaFree(ctx->d_pos);
+    cudaFree(ctx->d_sort_keys); cudaFree(ctx->d_sort_idx); cudaFree(ctx->d_tabmem);
+    ctx->d_values = ctx->d_loss = nullptr; ctx->d_pos = nullptr;
+    ctx->d_sort_keys = nullptr; ctx->d_sort_idx = nullptr; ctx->d_tabmem = nullptr;
+    ctx->hist_cap = 0; ctx->sort_cap = 0; ctx->tabmem_bytes = 0;
+    ctx->history_ready = false; ctx->n_trials = 0;
+    return KB_OK;
+}
+
+extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (ctx->D == 0) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_set_history: call kb_space_set first");
+    if (n_trials < 0 || n_trials > (1 << 22))
+        return kb_fail(ctx, KB_ERR_UNSUPPORTED, "kb_tpe_set_history: n_trials=%lld outside [0, 2^22]", (long long)n_trials);
+    if (n_trials > 0 && (!values || !loss)) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_history: NULL buffer");
+    const int n = (int)n_trials, D = ctx->D;
+    cudaStream_t s = ctx->stream;
+    ctx->history_ready = false;
+
+    if (n > ctx->hist_cap) {
+        cudaFree(ctx->d_values); cudaFree(ctx->d_loss); cudaFree(ctx->d_pos);
+        ctx->d_values = ctx->d_loss = nullptr; ctx->d_pos = nullptr;
+        int64_t cap = n + n / 4 + 64;
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_values, sizeof(double) * (size_t)cap * D));
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_loss, sizeof(double) * (size_t)cap));
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_pos, sizeof(int32_t) * 2 * (size_t)cap));
+        ctx->hist_cap = cap;
+    }
+    const int npad = next_pow2((int64_t)n + 1);
+    const int Kcap = pad_to(n + 1, KB_TABLE_PAD);
+    const int slots = ctx->n_numeric > 0 ? ctx->n_numeric : 1;
+    if ((int64_t)npad * 2 * slots > ctx->sort_cap) {
+        cudaFree(ctx->d_sort_keys); cudaFree(ctx->d_sort_idx);
+        ctx->d_sort_keys = nullptr; ctx->d_sort_idx = nullptr;
+        ctx->sort_cap = (int64_t)npad * 2 * slots;
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_sort_keys, sizeof(double) * (size_t)ctx->sort_cap));
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_sort_idx, sizeof(uint32_t) * (size_t)ctx->sort_cap));
+    }
+    // table arena: per numeric dim and side 4 f64 arrays + 1 float4 array of Kcap; per categorical dim 3 f64 + 1 i32 of C
+    size_t bytes = 0;
+    for (int d = 0; d < D; d++) {
+        const KbDim &k = ctx->h_dims[(size_t)d];
+        if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
+        else bytes += 2 * (size_t)Kcap * (4 * sizeof(double) + sizeof(float4));
+    }
+    if (bytes > ctx->tabmem_bytes) {
+        cudaFree(ctx->d_tabmem); ctx->d_tabmem = nullptr;
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_tabmem, bytes));
+        ctx->tabmem_bytes = bytes;
+    }
+    char *p = (char *)ctx->d_tabmem;
+    for (int d = 0; d < D; d++) {
+        KbDim &k = ctx->h_dims[(size_t)d];
+        if (k.kind == KB_CATEGORICAL) {
+            size_t c = (size_t)pad_to(k.n_choices, 32);
+            k.cat_p[0] = (double *)p; p += c * sizeof(double);
+            k.cat_p[1] = (double *)p; p += c * sizeof(double);
+            k.cat_score = (double *)p; p += c * sizeof(double);
+            k.cat_rank = (int32_t *)p; p += c * sizeof(double);
+        } else {
+            for (int side = 0; side < 2; side++) {
+                k.tab[side] = (float4 *)p; p += (size_t)Kcap * sizeof(float4);
+                k.mu[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
+                k.sigma[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
+                k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
+                k.logc[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
+            }
+        }
+    }
+    KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_dims, ctx->h_dims.data(), sizeof(KbDim) * (size_t)D, cudaMemcpyHostToDevice, s));
+    if (n > 0) {
+        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_values, values, sizeof(double) * (size_t)n * D, cudaMemcpyHostToDevice, s));
+        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_loss, loss, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, s));
+    }
+    const int nb = [&] { int a = (int)ceil(0.1 * (double)n); return a > 25 ? 25 : a; }();
+    split_kernel<<<1, BUILD_THREADS, 0, s>>>(ctx->d_loss, n, npad, ctx->d_sort_keys, ctx->d_sort_idx, ctx->d_pos);
+    KB_LAUNCH_CHECK(ctx);
+    if (ctx->n_numeric > 0) {
+        // numeric dims in slot order = cont and quant lists merged by numeric_slot
+        std::vector<int> numeric((size_t)ctx->n_numeric);
+        for (int d = 0; d < D; d++) if (ctx->h_dims[(size_t)d].numeric_slot >= 0) numeric[(size_t)ctx->h_dims[(size_t)d].numeric_slot] = d;
+        int *d_numeric = nullptr;
+        KB_CUDA(ctx, cudaMallocAsync(&d_numeric, sizeof(int) * numeric.size(), s));
+        KB_CUDA(ctx, cudaMemcpyAsync(d_numeric, numeric.data(), sizeof(int) * numeric.size(), cudaMemcpyHostToDevice, s));
+        parzen_kernel<<<dim3((unsigned)ctx->n_numeric, 2), BUILD_THREADS, 0, s>>>(
+            ctx->d_dims, d_numeric, ctx->d_values, n, D, nb, ctx->d_pos, npad, ctx->d_sort_keys, ctx->d_sort_idx);
+        KB_LAUNCH_CHECK(ctx);
+        KB_CUDA(ctx, cudaStreamSynchronize(s));  // `numeric` must outlive the async copy
+        cudaFreeAsync(d_numeric, s);
+    }
+    if (ctx->n_cat > 0) {
+        categorical_kernel<<<ctx->n_cat, 128, 0, s>>>(ctx->d_dims, ctx->d_cat_dims, ctx->d_values, n, D, nb, ctx->d_pos);
+        KB_LAUNCH_CHECK(ctx);
+    }
+    // bring back K / Kpad (the pointers are unchanged) so that launches can be sized on the host
+    KB_CUDA(ctx, cudaMemcpyAsync(ctx->h_dims.data(), ctx->d_dims, sizeof(KbDim) * (size_t)D, cudaMemcpyDeviceToHost, s));
+    KB_CUDA(ctx, cudaStreamSynchronize(s));
+    ctx->n_trials = n;
+    ctx->n_below = nb;
+    ctx->history_ready = true;
+    return KB_OK;
+}
+
+extern "C" int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, double *w, double *mu, double *sigma,
+                                 int cap, double *p_accept) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_get_parzen: no history set");
+    if (param < 0 || param >= ctx->D || (side != 0 && side != 1))
+        return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_get_parzen: param/side out of range");
+    const KbDim &k = ctx->h_dims[(size_t)param];
+    const int n = k.K[side];
+    if (K) *K = n;
+    if (cap < n) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_get_parzen: cap=%d < K=%d", cap, n);
+    if (k.kind == KB_CATEGORICAL) {
+        if (w) KB_CUDA(ctx, cudaMemcpy(w, k.cat_p[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+        if (p_accept) *p_accept = 1.0;
+        return KB_OK;
+    }
+    if (w) KB_CUDA(ctx, cudaMemcpy(w, k.w[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+    if (mu) KB_CUDA(ctx, cudaMemcpy(mu, k.mu[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+    if (sigma) KB_CUDA(ctx, cudaMemcpy(sigma, k.sigma[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
+    if (p_accept) *p_accept = k.p_accept[side];
+    return KB_OK;
+}

@@ -1,0 +1,186 @@
+"""TPE parity on the GPU (through the C ABI): Parzen tables bit-exact, scores within 1e-5 relative of the
+FP64 oracle, selected candidates identical.  Tolerance: |gpu - ref| <= 1e-5 * max(1, |ref|) (north_star)."""
+import os
+
+import numpy as np
+import pytest
+
+import _oracle as O
+import katib_b200 as kb
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = kb.Context(0)
+    yield c
+    c.close()
+
+
+def rel_err(got, ref):
+    return np.max(np.abs(got - ref) / np.maximum(1.0, np.abs(ref)))
+
+
+def make_history(rng, n, kinds, lows, highs, steps, nch):
+    cols = []
+    for k, lo, hi, st, c in zip(kinds, lows, highs, steps, nch):
+        if k == kb.KB_UNIFORM:
+            cols.append(rng.uniform(lo, hi, n))
+        elif k == kb.KB_INT:
+            cols.append(np.floor(rng.uniform(lo, hi + 1, n)))
+        elif k == kb.KB_STEP_INT:
+            cols.append(lo + st * np.floor(rng.uniform(0, (hi - lo) / st + 1, n)))
+        elif k == kb.KB_DISCRETE:
+            cols.append(lo + st * np.floor(rng.uniform(0, (hi - lo) / st + 1, n)))
+        else:
+            cols.append(np.floor(rng.uniform(0, c, n)))
+    v = np.stack(cols, axis=1)
+    return v
+
+
+def working_domain(k, lo, hi, st):
+    """(low, high, q, shift) of sampleNumerical for a distribution kind"""
+    if k == kb.KB_UNIFORM:
+        return lo, hi, 0.0, 0.0
+    if k == kb.KB_INT:
+        return lo - 0.5, hi + 0.5, 1.0, 0.0
+    if k == kb.KB_STEP_INT:
+        return lo - 0.5 * st, hi + 0.5 * st, st, 0.0
+    return -0.5 * st, (hi - lo) + 0.5 * st, st, lo
+
+
+def oracle_scores(kinds, lows, highs, steps, nch, vals, loss, cand):
+    out = np.zeros_like(cand)
+    best = []
+    for d, (k, lo, hi, st, c) in enumerate(zip(kinds, lows, highs, steps, nch)):
+        if k == kb.KB_CATEGORICAL:
+            sc, b = O.tpe_score_categorical(cand[:, d], vals[:, d], loss, c)
+        else:
+            wl, wh, q, sh = working_domain(k, lo, hi, st)
+            sc, b = O.tpe_score_numeric(cand[:, d], vals[:, d] - sh, loss, wl, wh, q)
+        out[:, d] = sc
+        best.append(b)
+    return out, best
+
+
+MIXED = dict(
+    kinds=[kb.KB_UNIFORM, kb.KB_INT, kb.KB_CATEGORICAL, kb.KB_DISCRETE, kb.KB_STEP_INT, kb.KB_UNIFORM, kb.KB_CATEGORICAL],
+    lows=[-1.5, -10, 0, 0.0, 0, 1e-3, 0], highs=[5.5, 10, 0, 16.0, 30, 3e-3, 0], steps=[0, 0, 0, 0.25, 3, 0, 0],
+    nch=[0, 0, 3, 0, 0, 0, 12])
+
+
+def sample_candidates(rng, n, sp, vals):
+    """working-domain candidates: continuous uniform, quantised on the grid (shifted for DISCRETE), categorical index"""
+    cols = []
+    for d, (k, lo, hi, st, c) in enumerate(zip(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])):
+        if k == kb.KB_UNIFORM:
+            cols.append(rng.uniform(lo, hi, n))
+        elif k == kb.KB_CATEGORICAL:
+            cols.append(np.floor(rng.uniform(0, c, n)))
+        else:
+            wl, wh, q, sh = working_domain(k, lo, hi, st)
+            x = rng.uniform(wl, wh, n)
+            cols.append(np.round(x / q) * q)
+    return np.stack(cols, axis=1)
+
+
+@pytest.mark.parametrize("n_trials", [0, 1, 9, 10, 24, 25, 26, 100, 1000, 3000])
+def test_parzen_tables_bit_exact(ctx, n_trials):
+    rng = np.random.Generator(np.random.PCG64(100 + n_trials))
+    sp = MIXED
+    ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    vals = make_history(rng, n_trials, sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    loss = rng.normal(size=n_trials)
+    if n_trials >= 26:
+        loss[5] = loss[17]  # a tie in the loss: stable order decides
+    ctx.tpe_set_history(vals.reshape(n_trials, len(sp["kinds"])), loss)
+    for d, (k, lo, hi, st, c) in enumerate(zip(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])):
+        if k == kb.KB_CATEGORICAL:
+            pl, pg = O.categorical_tables(vals[:, d], loss, c)
+            assert np.array_equal(ctx.tpe_get_parzen(d, 0)[0], pl)
+            assert np.array_equal(ctx.tpe_get_parzen(d, 1)[0], pg)
+            continue
+        wl, wh, q, sh = working_domain(k, lo, hi, st)
+        below, above = O.tpe_split(vals[:, d] - sh, loss)
+        for side, obs in ((0, below), (1, above)):
+            w, mu, sg = O.parzen_build(obs, wl, wh)
+            gw, gmu, gsg, pa = ctx.tpe_get_parzen(d, side)
+            assert np.array_equal(gmu, mu) and np.array_equal(gsg, sg) and np.array_equal(gw, w), (d, side)
+            ref_pa = sum(w[j] * (O.lib().kbo_normal_cdf(wh, mu[j], sg[j]) - O.lib().kbo_normal_cdf(wl, mu[j], sg[j]))
+                         for j in range(len(w)))
+            assert abs(pa - ref_pa) <= 1e-14 * abs(ref_pa)
+
+
+@pytest.mark.parametrize("n_trials,n_cand", [(10, 24), (100, 24), (100, 1), (300, 5000), (1000, 2049), (2500, 777)])
+def test_scores_and_winners_mixed(ctx, n_trials, n_cand):
+    rng = np.random.Generator(np.random.PCG64(7 * n_trials + n_cand))
+    sp = MIXED
+    ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    vals = make_history(rng, n_trials, sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    loss = (vals[:, 0] - 1.0) ** 2 + 0.05 * (vals[:, 1] - 3) ** 2 + (vals[:, 2] != 1) + rng.normal(0, 0.5, n_trials)
+    ctx.tpe_set_history(vals, loss)
+    cand = sample_candidates(rng, n_cand, sp, vals)
+    ref, best = oracle_scores(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"], vals, loss, cand)
+    got = ctx.tpe_scores(cand)
+    for d in range(len(sp["kinds"])):
+        assert rel_err(got[:, d], ref[:, d]) < TOL, (d, rel_err(got[:, d], ref[:, d]))
+    idx, val, sc = ctx.tpe_score_select(cand, index_offset=1000)
+    assert list(idx - 1000) == best
+    for d, k in enumerate(sp["kinds"]):
+        x = cand[best[d], d]
+        if k == kb.KB_DISCRETE:
+            x = min(max(x + sp["lows"][d], sp["lows"][d]), sp["highs"][d])
+        assert val[d] == x
+        assert abs(sc[d] - ref[best[d], d]) <= 1e-9 * max(1.0, abs(ref[best[d], d]))
+
+
+def test_config3_shape_reduced(ctx):
+    """BASELINE configs[2] shape (20-dim continuous, 1k trials) at 32768 candidates -- what the oracle finishes fast."""
+    rng = np.random.Generator(np.random.PCG64(3))
+    D, n, nc = 20, 1000, 32768
+    s = np.linspace(0.5, 4.0, D)
+    lows, highs = -5 * s, 5 * s
+    ctx.space_set([kb.KB_UNIFORM] * D, lows, highs)
+    vals = rng.uniform(lows, highs, (n, D))
+    loss = np.sum((vals / s) ** 2, axis=1) + rng.normal(0, 1, n)
+    ctx.tpe_set_history(vals, loss)
+    cand = rng.uniform(lows, highs, (nc, D))
+    got = ctx.tpe_scores(cand)
+    idx, val, sc = ctx.tpe_score_select(cand)
+    worst = 0.0
+    for d in range(D):
+        ref, b = O.tpe_score_numeric(cand[:, d], vals[:, d], loss, lows[d], highs[d])
+        worst = max(worst, rel_err(got[:, d], ref))
+        assert idx[d] == b and val[d] == cand[b, d]
+    assert worst < TOL, worst
+    print("config3-shape max rel err", worst)
+
+
+def test_duplicates_first_index_wins(ctx):
+    rng = np.random.Generator(np.random.PCG64(11))
+    ctx.space_set([kb.KB_UNIFORM, kb.KB_INT], [0.0, 0], [1.0, 7])
+    vals = np.stack([rng.uniform(0, 1, 200), np.floor(rng.uniform(0, 8, 200))], axis=1)
+    loss = (vals[:, 0] - 0.3) ** 2 + 0.01 * vals[:, 1]
+    ctx.tpe_set_history(vals, loss)
+    base = np.stack([rng.uniform(0, 1, 500), np.floor(rng.uniform(0, 8, 500))], axis=1)
+    cand = np.concatenate([base, base[::-1], base])  # every value three times
+    r0, b0 = O.tpe_score_numeric(cand[:, 0], vals[:, 0], loss, 0.0, 1.0)
+    r1, b1 = O.tpe_score_numeric(cand[:, 1], vals[:, 1], loss, -0.5, 7.5, 1.0)
+    idx, val, sc = ctx.tpe_score_select(cand)
+    assert list(idx) == [b0, b1]
+
+
+def test_call_order_and_errors(ctx):
+    c2 = kb.Context(0)
+    with pytest.raises(kb.KbError):
+        c2.tpe_set_history(np.zeros((3, 2)), np.zeros(3))  # no space yet
+    c2.space_set([kb.KB_UNIFORM], [0.0], [1.0])
+    with pytest.raises(kb.KbError):
+        c2.tpe_scores(np.zeros((4, 1)))  # no history yet
+    with pytest.raises(kb.KbError):
+        c2.space_set([kb.KB_DISCRETE], [0.0], [1.0], [0.0])  # step must be > 0
+    with pytest.raises(kb.KbError):
+        c2.space_set([kb.KB_UNIFORM], [2.0], [1.0])
+    c2.close()
