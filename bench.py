@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""bench.py -- TPE candidates scored/s on BASELINE.json's headline workload.
+
+Workload (BASELINE configs[4]): TPE, 50 parameters (20 uniform, 5 int [0,63], 5 discrete-uniform
+q=0.25 on [0,16], 20 categorical with 2..16 choices), 10 000-trial history, 64 Mi candidates per GetSuggestions,
+sharded over N GPUs (strong scaling: the candidate set is fixed, each rank scores 1/N of it, one NCCL collective
+picks the winners).  A "step" = one full scoring+selection pass over the candidate set.
+
+  value : candidates/s with the rank's candidate slice already resident in HBM (kb_tpe_score_select_device)
+  e2e   : the same through the host-buffer C-ABI call (kb_tpe_score_select): every step copies the slice from pinned
+          host memory (double-buffered H2D inside the call) and reads the winners back
+  roofline : per kernel class, CUDA-event durations measured live inside the library (kb_profile); the SFU peak is
+          measured in this run by kb_peak_measure (MEASURED_PEAKS.json has no MUFU figure)
+  cpu_baseline : the CPU oracle (port of goptuna's algorithm, oracle/tpe.c) on a bounded candidate sample
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--cand LOG2]
+  N > 1: launched by torch.distributed.run, one rank per GPU.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+N_HISTORY = 10_000
+CAT_CHOICES = [2, 3, 4, 6, 8, 12, 16]
+
+
+def workload_space():
+    import katib_b200 as kb
+    kinds, lows, highs, steps, nch = [], [], [], [], []
+    for i in range(20):
+        s = 0.5 + 0.25 * i
+        kinds.append(kb.KB_UNIFORM); lows.append(-5.0 * s); highs.append(5.0 * s); steps.append(0.0); nch.append(0)
+    for i in range(5):
+        kinds.append(kb.KB_INT); lows.append(0.0); highs.append(63.0); steps.append(0.0); nch.append(0)
+    for i in range(5):
+        kinds.append(kb.KB_DISCRETE); lows.append(0.0); highs.append(16.0); steps.append(0.25); nch.append(0)
+    for i in range(20):
+        kinds.append(kb.KB_CATEGORICAL); lows.append(0.0); highs.append(0.0); steps.append(0.0)
+        nch.append(CAT_CHOICES[i % len(CAT_CHOICES)])
+    return kinds, np.array(lows), np.array(highs), np.array(steps), nch
+
+
+def workload_history(kinds, lows, highs, steps, nch, n=N_HISTORY, seed=5):
+    import katib_b200 as kb
+    rng = np.random.Generator(np.random.PCG64(seed))
+    cols, loss = [], np.zeros(n)
+    for d, k in enumerate(kinds):
+        if k == kb.KB_UNIFORM:
+            c = rng.uniform(lows[d], highs[d], n)
+            loss += (c / (highs[d] / 5.0)) ** 2
+        elif k == kb.KB_INT:
+            c = np.floor(rng.uniform(lows[d], highs[d] + 1, n))
+            loss += ((c - 20.0) / 16.0) ** 2
+        elif k == kb.KB_DISCRETE:
+            c = lows[d] + steps[d] * np.floor(rng.uniform(0, (highs[d] - lows[d]) / steps[d] + 1, n))
+            loss += ((c - 5.0) / 4.0) ** 2
+        else:
+            c = np.floor(rng.uniform(0, nch[d], n))
+            loss += 0.3 * (c != (d % nch[d]))
+        cols.append(c)
+    loss += rng.normal(0, 1.0, n)
+    return np.stack(cols, axis=1), loss
+
+
+def device_candidates(torch, kinds, lows, highs, steps, nch, n, seed, device):
+    """Synthetic candidates in the sampler's working domain, generated on the device by torch (plumbing):
+    uniform over each parameter's range; quantised parameters on their grid; categorical = choice index."""
+    import katib_b200 as kb
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    out = torch.empty((n, len(kinds)), dtype=torch.float64, device=device)
+    rows = 1 << 20
+    for r0 in range(0, n, rows):
+        m = min(rows, n - r0)
+        u = torch.rand((m, len(kinds)), generator=g, device=device, dtype=torch.float64)
+        for d, k in enumerate(kinds):
+            if k == kb.KB_UNIFORM:
+                u[:, d] = lows[d] + u[:, d] * (highs[d] - lows[d])
+            elif k == kb.KB_INT:
+                u[:, d] = torch.floor(lows[d] + u[:, d] * (highs[d] - lows[d] + 1))
+            elif k == kb.KB_DISCRETE:  # working domain is shifted to [0, high-low]
+                u[:, d] = steps[d] * torch.floor(u[:, d] * ((highs[d] - lows[d]) / steps[d] + 1))
+            else:
+                u[:, d] = torch.floor(u[:, d] * nch[d])
+        out[r0:r0 + m] = u
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 9 for i in range(4) if r[5 + i].lower().startswith("active")})
+        pw = [float(r[3]) for r in self.rows if len(r) >= 9 and r[3].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm)}
+
+
+def oracle_score_block(O, kinds, lows, highs, steps, nch, vals, loss, cand):
+    """The CPU port scoring every parameter of a candidate block (returns the per-parameter winners)."""
+    import katib_b200 as kb
+    best = []
+    for d, k in enumerate(kinds):
+        if k == kb.KB_CATEGORICAL:
+            _, b = O.tpe_score_categorical(cand[:, d], vals[:, d], loss, nch[d])
+        elif k == kb.KB_UNIFORM:
+            _, b = O.tpe_score_numeric(cand[:, d], vals[:, d], loss, lows[d], highs[d])
+        elif k == kb.KB_INT:
+            _, b = O.tpe_score_numeric(cand[:, d], vals[:, d], loss, lows[d] - 0.5, highs[d] + 0.5, 1.0)
+        else:
+            q = steps[d]
+            _, b = O.tpe_score_numeric(cand[:, d], vals[:, d] - lows[d], loss, -0.5 * q, (highs[d] - lows[d]) + 0.5 * q, q)
+        best.append(b)
+    return best
+
+
+def cpu_baseline(kinds, lows, highs, steps, nch, vals, loss, n_sample, threads, seed=77):
+    """candidates/s of the CPU port (oracle/tpe.c) on n_sample candidates, split over `threads` host threads."""
+    import _oracle as O
+    O.lib()
+    import katib_b200 as kb
+    rng = np.random.Generator(np.random.PCG64(seed))
+    cols = []
+    for d, k in enumerate(kinds):
+        u = rng.random(n_sample)
+        if k == kb.KB_UNIFORM:
+            cols.append(lows[d] + u * (highs[d] - lows[d]))
+        elif k == kb.KB_INT:
+            cols.append(np.floor(lows[d] + u * (highs[d] - lows[d] + 1)))
+        elif k == kb.KB_DISCRETE:
+            cols.append(steps[d] * np.floor(u * ((highs[d] - lows[d]) / steps[d] + 1)))
+        else:
+            cols.append(np.floor(u * nch[d]))
+    cand = np.stack(cols, axis=1)
+    parts = np.array_split(np.arange(n_sample), threads)
+    t0 = time.perf_counter()
+    if threads == 1:
+        oracle_score_block(O, kinds, lows, highs, steps, nch, vals, loss, cand)
+    else:
+        ths = [threading.Thread(target=oracle_score_block, args=(O, kinds, lows, highs, steps, nch, vals, loss, cand[p]))
+               for p in parts if len(p)]
+        [t.start() for t in ths]
+        [t.join() for t in ths]
+    dt = time.perf_counter() - t0
+    return n_sample / dt, dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--cand", type=int, default=26, help="log2 of the candidate count (26 = 64 Mi, the headline)")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="candidates in the CPU-baseline sample (0 = auto)")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    n_total = 1 << args.cand
+    kinds, lows, highs, steps, nch = workload_space()
+    vals, loss = workload_history(kinds, lows, highs, steps, nch)
+    D = len(kinds)
+    n_below = min(int(np.ceil(0.1 * N_HISTORY)), 25)
+    K_l, K_g = n_below + 1, N_HISTORY - n_below + 1
+    config = {"workload": "TPE 50-dim mixed (20 uniform, 5 int[0,63], 5 discrete q=0.25 on [0,16], 20 categorical), "
+                          f"{N_HISTORY}-trial history, 2^{args.cand} candidates per GetSuggestions, sharded across N GPUs",
+              "baseline_config": "configs[4]", "n_candidates": n_total, "n_params": D, "n_trials": N_HISTORY,
+              "parallelism": f"candidate-sharded x{world}", "l2": "inputs larger than L2 (per-step candidate slice >= 400 MB)"}
+
+    # ------------------------------------------------------------------ reference arm: CPU port on host cores
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cores = os.cpu_count() or 1
+        n_sample = args.cpu_sample or 256 * cores
+        for _ in range(max(1, args.warmup)):
+            cpu_baseline(kinds, lows, highs, steps, nch, vals, loss, max(cores, n_sample // 8), cores)
+        rates, t_tot = [], 0.0
+        for _ in range(args.steps):
+            r, dt = cpu_baseline(kinds, lows, highs, steps, nch, vals, loss, n_sample, cores)
+            rates.append(r); t_tot += dt
+        v = n_sample * args.steps / t_tot
+        print(json.dumps({
+            "impl": "reference", "metric": "tpe_candidates_scored_per_s", "value": v, "unit": "candidates/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config,
+            "cpu_baseline": {"value": v, "unit": "candidates/s", "cores": cores, "kind": "port",
+                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history per step "
+                                       "(goptuna is Go and un-vendored: the oracle port stands in; it scores one "
+                                       "candidate block per host thread)"},
+            "e2e": {"value": v, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    # ------------------------------------------------------------------ our arm
+    import torch
+    import katib_b200 as kb
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    ctx = kb.Context(local_rank)
+    if world > 1:
+        uid = [kb.Context.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(world, rank, uid[0])
+    ctx.space_set(kinds, lows, highs, steps, nch)
+    ctx.tpe_set_history(vals, loss)
+    n_local = n_total // world
+    offset = rank * n_local
+    cand = device_candidates(torch, kinds, lows, highs, steps, nch, n_local, 55 + rank, dev)
+    torch.cuda.synchronize()
+    stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for _ in range(steps):
+            res = fn()
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms, wall * 1e3], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1]) / 1e3
+        return ms, wall, res
+
+    step_dev = lambda: ctx.tpe_score_select_device(n_local, cand.data_ptr(), offset)
+    peaks = {}
+    if rank == 0:
+        peaks = {"mufu_ex2_gops": ctx.peak(0), "fp32_gfma": ctx.peak(1), "fp64_gfma": ctx.peak(2), "hbm_write_gbs": ctx.peak(3)}
+    for _ in range(args.warmup):
+        step_dev()
+    launches0 = ctx.launch_count()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ctx.profile(True)
+    ms, wall, res = timed(step_dev, args.steps)
+    prof = {k: ctx.profile_read(k) for k in range(4)}
+    ctx.profile(False)
+    clk = clocks.stop() if rank == 0 else None
+    launches = ctx.launch_count() - launches0
+    value = n_total * args.steps / (ms * 1e-3)
+
+    # ---- end to end: host buffers through the public C-ABI call
+    e2e = None
+    if not args.no_e2e:
+        try:
+            host = torch.empty((n_local, D), dtype=torch.float64, pin_memory=True)
+            host.copy_(cand)
+            pinned_note = "full slice pinned"
+        except RuntimeError as ex:  # not enough pinnable memory on this box
+            host, pinned_note = None, f"pinned allocation failed: {str(ex)[:80]}"
+        if host is not None:
+            torch.cuda.synchronize()
+            step_host = lambda: ctx.tpe_score_select_ptr(n_local, host.data_ptr(), offset)
+            for _ in range(args.warmup):
+                step_host()
+            ms_h, wall_h, res_h = timed(step_host, args.steps)
+            assert all(np.array_equal(a, b) for a, b in zip(res, res_h)), "e2e winners differ from the device-resident run"
+            e2e = {"value": n_total * args.steps / wall_h, "unit": "candidates/s",
+                   "h2d_bytes_per_step": int(n_local * D * 8 * world), "d2h_bytes_per_step": int(D * 24 * world),
+                   "ms_per_step": 1e3 * wall_h / args.steps, "timing": "host wall clock around the blocking C-ABI call, "
+                   "max over ranks", "note": pinned_note}
+        else:
+            e2e = {"value": None, "unit": "candidates/s", "note": pinned_note}
+
+    if rank != 0:
+        return
+    # ---- roofline from the live per-kernel event times (this rank's slice; every rank does the same work)
+    n_cont, n_quant = 20, 10
+    ce_cont = float(n_local) * n_cont * (K_l + K_g) * args.steps
+    ce_quant = float(n_local) * n_quant * (K_l + K_g) * args.steps
+    names = ["tpe_stage_kernel", "tpe_score_cont_kernel", "tpe_score_quant_kernel", "tpe_rescore+pick"]
+    tot = sum(p[0] for p in prof.values()) or 1.0
+    kern = []
+    for k in range(4):
+        ms_k, n_k = prof[k]
+        ent = {"name": names[k], "ms_total": ms_k, "launches": n_k, "share_of_kernel_time": ms_k / tot}
+        if k == 1 and ms_k > 0:
+            a = ce_cont / (ms_k * 1e-3) / 1e9
+            ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
+                       frac=a / peaks["mufu_ex2_gops"])
+        if k == 2 and ms_k > 0:
+            a = ce_quant / (ms_k * 1e-3) / 1e9
+            ent.update(bound="sfu", unit="G CDF-pair evals/s (2 exp = 2 MUFU.EX2 each, algorithmic)", achieved=a,
+                       peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2))
+        if k == 0 and ms_k > 0:
+            bytes_alg = float(n_local) * D * 8 * args.steps + float(n_local) * (n_cont * 8 + n_quant * 16) * args.steps
+            a = bytes_alg / (ms_k * 1e-3) / 1e9
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+                os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+            ent.update(bound="hbm", unit="GB/s", achieved=a, peak=mp, frac=a / mp)
+        kern.append(ent)
+    dom = max((e for e in kern if "frac" in e), key=lambda e: e["ms_total"])
+    roofline = {"bound": dom["bound"], "achieved": dom["achieved"], "peak": dom["peak"], "unit": dom["unit"],
+                "frac": dom["frac"], "traffic": None, "kernel": dom["name"],
+                "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel on this GPU in this run (of measured); "
+                               "MEASURED_PEAKS.json has HBM and bf16 only",
+                "kernels": kern, "measured_peaks": peaks}
+    cores = 1
+    n_sample = args.cpu_sample or 384
+    cpu_v, cpu_dt = cpu_baseline(kinds, lows, highs, steps, nch, vals, loss, n_sample, cores)
+    out = {"metric": "tpe_candidates_scored_per_s", "value": value, "unit": "candidates/s", "n_gpus": world,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "f32 (hi/lo-split inputs, f64 accumulation; winners re-scored in f64)",
+           "data": "synthetic", "config": config, "clocks": clk, "e2e": e2e, "gpu_launches": launches,
+           "roofline": roofline,
+           "cpu_baseline": {"value": cpu_v, "unit": "candidates/s", "cores": cores, "kind": "port",
+                            "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
+                                      "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
+           "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

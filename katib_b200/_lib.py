@@ -80,6 +80,8 @@ def lib():
         "kb_random_fill": ([vp, u64, u64, i64, vp], i32),
         "kb_peak_measure": ([vp, i32, C.POINTER(dbl)], i32),
         "kb_launch_count": ([vp], i64),
+        "kb_profile": ([vp, i32], i32),
+        "kb_profile_read": ([vp, i32, C.POINTER(dbl), C.POINTER(i64)], i32),
     }
     for name, (args, res) in sig.items():
         f = getattr(L, name)
@@ -139,6 +141,14 @@ class Context:
         self._ck(lib().kb_peak_measure(self._h, which, C.byref(v)))
         return v.value
 
+    def profile(self, enable):
+        self._ck(lib().kb_profile(self._h, 1 if enable else 0))
+
+    def profile_read(self, kernel_class):
+        ms, n = C.c_double(), C.c_int64()
+        self._ck(lib().kb_profile_read(self._h, kernel_class, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
     # -- comm
     @staticmethod
     def unique_id():
@@ -165,7 +175,6 @@ class Context:
     def tpe_set_history(self, values, loss):
         values, loss = _f64(values), _f64(loss)
         n = len(loss)
-        assert values.shape == (n, self.D) or n == 0
         self._ck(lib().kb_tpe_set_history(self._h, n, _ptr(values), _ptr(loss)))
 
     def tpe_get_parzen(self, param, side, cap=None):

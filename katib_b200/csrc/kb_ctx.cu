@@ -6,6 +6,7 @@
 #include "kb_internal.cuh"
 
 static thread_local std::string g_create_err;
+static void prof_drain(kb_ctx *ctx);
 
 int kb_fail(const kb_ctx *ctx, int code, const char *fmt, ...) {
     char buf[1024];
@@ -76,6 +77,8 @@ extern "C" int kb_destroy(kb_ctx *ctx) {
             if (ctx->ev_h2d[i]) cudaEventDestroy(ctx->ev_h2d[i]);
             if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
         }
+        prof_drain(ctx);
+        for (auto e : ctx->prof_pool) cudaEventDestroy(e);
         if (ctx->stream) cudaStreamDestroy(ctx->stream);
         if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     }
@@ -97,6 +100,39 @@ extern "C" int kb_device_info(const kb_ctx *ctx, int64_t out[5]) {
 
 extern "C" void *kb_stream(const kb_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 extern "C" int64_t kb_launch_count(const kb_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+static void prof_drain(kb_ctx *ctx) {
+    for (int k = 0; k < KB_PROF_N; k++) {
+        for (auto &pr : ctx->prof_pending[k]) {
+            float ms = 0.f;
+            cudaEventSynchronize(pr.second);
+            if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) { ctx->prof_ms[k] += ms; ctx->prof_launches[k]++; }
+            ctx->prof_pool.push_back(pr.first);
+            ctx->prof_pool.push_back(pr.second);
+        }
+        ctx->prof_pending[k].clear();
+    }
+}
+
+extern "C" int kb_profile(kb_ctx *ctx, int enable) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    prof_drain(ctx);
+    if (enable) for (int k = 0; k < KB_PROF_N; k++) { ctx->prof_ms[k] = 0; ctx->prof_launches[k] = 0; }
+    ctx->profile = enable != 0;
+    return KB_OK;
+}
+
+extern "C" int kb_profile_read(kb_ctx *ctx, int kernel_class, double *ms_total, int64_t *launches) {
+    if (!ctx || kernel_class < 0 || kernel_class >= KB_PROF_N) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    prof_drain(ctx);
+    if (ms_total) *ms_total = ctx->prof_ms[kernel_class];
+    if (launches) *launches = ctx->prof_launches[kernel_class];
+    return KB_OK;
+}
 
 extern "C" int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, const double *low,
                             const double *high, const double *step, const int32_t *n_choices) {

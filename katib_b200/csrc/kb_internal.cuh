@@ -60,6 +60,7 @@ struct KbWinner {                // per-parameter result (device + host mirror)
     double value;
 };
 
+#define KB_PROF_N 16
 struct KbComm;  // kb_comm.cu
 struct KbCma;   // kb_cmaes.cu
 
@@ -114,6 +115,29 @@ struct kb_ctx {
 
     KbComm *comm = nullptr;
     KbCma *cma = nullptr;
+
+    // per-kernel-class CUDA-event timing (kb_profile / kb_profile_read); off by default
+    bool profile = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_pending[KB_PROF_N];
+    std::vector<cudaEvent_t> prof_pool;
+    double prof_ms[KB_PROF_N] = {0};
+    int64_t prof_launches[KB_PROF_N] = {0};
+};
+
+// records an event pair around one launch on stream s when profiling is on
+struct KbProf {
+    kb_ctx *ctx; int id; cudaStream_t s; cudaEvent_t e0 = nullptr, e1 = nullptr;
+    KbProf(kb_ctx *c, int id_, cudaStream_t s_) : ctx(c), id(id_), s(s_) {
+        if (!ctx->profile) return;
+        auto take = [&]() { cudaEvent_t e; if (!ctx->prof_pool.empty()) { e = ctx->prof_pool.back(); ctx->prof_pool.pop_back(); } else cudaEventCreate(&e); return e; };
+        e0 = take(); e1 = take();
+        cudaEventRecord(e0, s);
+    }
+    ~KbProf() {
+        if (!e0) return;
+        cudaEventRecord(e1, s);
+        ctx->prof_pending[id].push_back({e0, e1});
+    }
 };
 
 // ---- error plumbing ---------------------------------------------------------------------------------

@@ -101,6 +101,7 @@ static int sobol_launch(kb_ctx *ctx, int dim, uint64_t first, int64_t n, const d
     const long long cap = wave * 8 / by > 0 ? wave * 8 / by : 1;
     if (bx > cap) bx = cap;
     dim3 grid((unsigned)bx, (unsigned)by);
+    KbProf pf(ctx, 4, s);
     sobol_fill_kernel<<<grid, SOBOL_DT * SOBOL_GROUPS, 0, s>>>(ctx->d_sobol_v, dim, first, n, d_low, d_high, d_out);
     KB_LAUNCH_CHECK(ctx);
     return KB_OK;

@@ -230,7 +230,7 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
             if (quant) {
                 double den = sqrt(2.0) * sg[j];
                 if (den < KB_EPS) den = KB_EPS;
-                float r = (float)((high - low) / den);  // 1 / (sqrt2 sigma_n)
+                float r = (float)(sqrt(LOG2E) * (high - low) / den);  // sqrt(log2 e) / (sqrt2 sigma_n)
                 e = make_float4(mh, r, (float)(-ml * (double)r), (float)w[j]);
             } else {
                 double s = sg[j] > KB_EPS ? sg[j] : KB_EPS;

@@ -285,6 +285,28 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
 // ---------------------------------------------------------------------------------------------------------
 #define SQ_R 4
 #define SQ_TILE (SC_THREADS * SQ_R)
+#define LN2F 0.6931471806f
+#define KINVF 0.8325546112f           // 1/sqrt(log2 e)
+#define QUANT_WIDE_THR 0.2402245f     // (b - a) <= 0.2 in erf units, scaled by sqrt(log2 e)
+
+__device__ __forceinline__ float kb_rcp(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// erfc(x) for x >= 0, argument pre-scaled: xs = sqrt(log2 e) x.  erfcx(x) = t P6(t), t = 1/(x+2) (near-minimax
+// fit, 3.6e-7 relative on [0, 6.6]); erfc = erfcx * 2^{-xs^2}.  1 MUFU.RCP + 1 MUFU.EX2 + 10 FP32 ops.
+__device__ __forceinline__ float erfc_pos_scaled(float xs) {
+    const float t = kb_rcp(fmaf(xs, KINVF, 2.0f));
+    float p = 1.219882546e+01f;
+    p = fmaf(p, t, -2.445210690e+01f);
+    p = fmaf(p, t, 1.361089618e+01f);
+    p = fmaf(p, t, 1.865695796e-01f);
+    p = fmaf(p, t, 2.333518575e+00f);
+    p = fmaf(p, t, 1.102339077e+00f);
+    p = fmaf(p, t, 5.649710102e-01f);
+    return (p * t) * kb_ex2(-xs * xs);
+}
 
 __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
@@ -318,6 +340,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
     double S[SQ_R], P0[SQ_R];
 #pragma unroll
     for (int r = 0; r < SQ_R; r++) S[r] = 0.0;
+    const float qn = (float)(dm.q / (dm.hi - dm.lo));
 
     for (int c = 0; c < nchunks; c++) {
         const int st = c % SC_STAGES;
@@ -332,15 +355,37 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
             for (int r = 0; r < SQ_R; r++) a32[r] = 0.f;
 #pragma unroll 2
             for (int j = 0; j < SC_GROUP; j++) {
-                const float4 e = tab[j0 + j];  // {mu_hi, r, -mu_lo*r, w}
+                const float4 e = tab[j0 + j];  // {mu_hi, r', -mu_lo*r', w},  r' = sqrt(log2 e) / (sqrt2 sigma_n)
+                // erfc arguments scaled by sqrt(log2 e): a' = k a, b' = k b, so that e^{-a^2} = 2^{-a'^2}
+                if (e.y * qn < QUANT_WIDE_THR) {
+                    // bin narrow against sigma (b - a <= 0.2): erfc(a) - erfc(b) would cancel, so integrate the
+                    // Gaussian over the bin by its Taylor series about the midpoint (Hermite terms to h^6)
 #pragma unroll
-                for (int r = 0; r < SQ_R; r++) {
-                    float a = fmaf((lh[r] - e.x) + ll[r], e.y, e.z);
-                    float b = fmaf((uh[r] - e.x) + ul[r], e.y, e.z);
-                    // Phi(b)-Phi(a) = (erfc(a)-erfc(b))/2; mirror to the side where erfc is small
-                    const bool flip = a + b < 0.f;
-                    const float a2 = flip ? -b : a, b2 = flip ? -a : b;
-                    a32[r] = fmaf(e.w, erfcf(a2) - erfcf(b2), a32[r]);
+                    for (int r = 0; r < SQ_R; r++) {
+                        const float a = fmaf((lh[r] - e.x) + ll[r], e.y, e.z);
+                        const float b = fmaf((uh[r] - e.x) + ul[r], e.y, e.z);
+                        const float m = 0.5f * (a + b), h = 0.5f * (b - a);
+                        const float mm = m * m;
+                        const float u = mm * LN2F, v = (h * h) * LN2F;
+                        const float c1 = fmaf(u, 0.6666666667f, -0.3333333333f);
+                        const float c2 = fmaf(fmaf(u, 0.1333333333f, -0.4f), u, 0.1f);
+                        const float c3 = fmaf(fmaf(fmaf(u, 0.0126984127f, -0.0952380952f), u, 0.1428571429f), u, -0.0238095238f);
+                        const float S = fmaf(fmaf(fmaf(c3, v, c2), v, c1), v, 1.0f);
+                        const float d2 = (h * (2.2567583342f * KINVF)) * S * kb_ex2(-mm);  // (4/sqrt(pi)) h S e^{-m^2}
+                        a32[r] = fmaf(e.w, d2, a32[r]);
+                    }
+                } else {
+#pragma unroll
+                    for (int r = 0; r < SQ_R; r++) {
+                        const float a = fmaf((lh[r] - e.x) + ll[r], e.y, e.z);
+                        const float b = fmaf((uh[r] - e.x) + ul[r], e.y, e.z);
+                        // Phi(b)-Phi(a) = (erfc(a)-erfc(b))/2; mirror so that b >= |a| (erfc small, relative accuracy kept)
+                        const bool flip = a + b < 0.f;
+                        const float a2 = flip ? -b : a, b2 = flip ? -a : b;
+                        const float ea = erfc_pos_scaled(fabsf(a2)), eb = erfc_pos_scaled(b2);
+                        const float ea2 = a2 < 0.f ? 2.0f - ea : ea;
+                        a32[r] = fmaf(e.w, ea2 - eb, a32[r]);
+                    }
                 }
             }
 #pragma unroll
@@ -556,18 +601,22 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
     kb_ctx *sc = ctx;
     const int D = ctx->D;
     KbSelect *sel = select ? ctx->d_sel : nullptr;
+    { KbProf pf(ctx, 0, s);
     tpe_stage_kernel<<<(n + ST_ROWS - 1) / ST_ROWS, ST_THREADS, 0, s>>>(ctx->d_dims, D, d_cand, n, ctx->chunk_cap,
                                                                         ctx->d_stage_cont, ctx->d_stage_quant,
                                                                         sc->d_slot_of_dim, sel, local_base, d_scores);
+    }
     KB_LAUNCH_CHECK(ctx);
     if (ctx->n_cont > 0) {
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
+        KbProf pf(ctx, 1, s);
         tpe_score_cont_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont, ctx->chunk_cap, n,
                                                           idx_base, D, sel, ctx->d_tie, sc->d_tie_score, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
     }
     if (ctx->n_quant > 0) {
         dim3 grid((unsigned)((n + SQ_TILE - 1) / SQ_TILE), (unsigned)ctx->n_quant);
+        KbProf pf(ctx, 2, s);
         tpe_score_quant_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant, ctx->chunk_cap,
                                                            n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
@@ -586,12 +635,14 @@ static int tpe_finish_selection(kb_ctx *ctx, long long idx_base, int64_t *out_in
                                 cudaStream_t s) {
     kb_ctx *sc = ctx;
     const int D = ctx->D;
+    KbProf *pf3 = new KbProf(ctx, 3, s);
     if (ctx->n_numeric > 0) {
         tpe_rescore_kernel<<<dim3((unsigned)ctx->n_numeric, RS_BLOCKS), RS_THREADS, 0, s>>>(
             ctx->d_dims, sc->d_numeric_dims, ctx->d_sel, ctx->d_tie, sc->d_tie_score, (KbPartial *)sc->d_partial);
         KB_LAUNCH_CHECK(ctx);
     }
     tpe_pick_kernel<<<(D + 127) / 128, 128, 0, s>>>(ctx->d_dims, D, ctx->d_sel, (const KbPartial *)sc->d_partial, ctx->d_win, idx_base);
+    delete pf3;
     KB_LAUNCH_CHECK(ctx);
     int world = 1, rank = 0;
     kb_comm_world(ctx, &world, &rank);

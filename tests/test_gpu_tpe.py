@@ -175,7 +175,7 @@ def test_duplicates_first_index_wins(ctx):
 def test_call_order_and_errors(ctx):
     c2 = kb.Context(0)
     with pytest.raises(kb.KbError):
-        c2.tpe_set_history(np.zeros((3, 2)), np.zeros(3))  # no space yet
+        c2.tpe_set_history(np.zeros((3, 2)), np.zeros(3))  # no space yet: KB_ERR_STATE
     c2.space_set([kb.KB_UNIFORM], [0.0], [1.0])
     with pytest.raises(kb.KbError):
         c2.tpe_scores(np.zeros((4, 1)))  # no history yet
@@ -184,3 +184,22 @@ def test_call_order_and_errors(ctx):
     with pytest.raises(kb.KbError):
         c2.space_set([kb.KB_UNIFORM], [2.0], [1.0])
     c2.close()
+
+
+def test_config5_shape_reduced(ctx):
+    """BASELINE configs[4] shape (50-dim mixed, 10k trials) at 4096 candidates; prints the worst relative error."""
+    import bench
+    kinds, lows, highs, steps, nch = bench.workload_space()
+    vals, loss = bench.workload_history(kinds, lows, highs, steps, nch)
+    ctx.space_set(kinds, lows, highs, steps, nch)
+    ctx.tpe_set_history(vals, loss)
+    rng = np.random.Generator(np.random.PCG64(55))
+    sp = dict(kinds=kinds, lows=lows, highs=highs, steps=steps, nch=nch)
+    cand = sample_candidates(rng, 4096, sp, vals)
+    ref, best = oracle_scores(kinds, lows, highs, steps, nch, vals, loss, cand)
+    got = ctx.tpe_scores(cand)
+    errs = np.array([rel_err(got[:, d], ref[:, d]) for d in range(len(kinds))])
+    print("config5-shape max rel err: cont %.2e quant %.2e cat %.2e" % (errs[:20].max(), errs[20:30].max(), errs[30:].max()))
+    assert errs.max() < TOL, errs
+    idx, val, sc = ctx.tpe_score_select(cand)
+    assert list(idx) == best
