@@ -161,7 +161,7 @@ int kb_random_fill(kb_ctx *ctx, uint64_t seed, uint64_t first_index, int64_t n, 
 
 /* ---- measurement helpers (used by bench.py and the profiles) ----------------------------------
  * which: 0 = MUFU.EX2 Gop/s, 1 = FP32 FFMA GFMA/s, 2 = FP64 DFMA GFMA/s, 3 = HBM write GB/s,
- * 4 = HBM copy GB/s.  Runs a saturating micro-kernel on the ctx's device and returns the rate. */
+ * 4 = HBM copy GB/s, 5 = FP32 GFMA/s through packed FFMA2.  Runs a saturating micro-kernel on the ctx's device and returns the rate. */
 int kb_peak_measure(kb_ctx *ctx, int which, double *out);
 /* Per-kernel-class device timing with CUDA events on the launching stream.  kb_profile(ctx, 1) starts
  * (and clears) the counters, kb_profile(ctx, 0) stops; kb_profile_read returns the summed duration and

@@ -25,16 +25,27 @@ struct KbDim {
     double *mu[2], *sigma[2], *w[2], *logc[2];  // logc = log(w / (sqrt(2pi) sigma p_accept))
     double p_accept[2];
     double L[2];              // max_j logc (fixed log-sum-exp shift)
-    // FP32 folded tables for the scoring kernels: float4 per component, Kpad entries
-    //   continuous: {mu_hi, c', m' = -mu_lo*c', k'}     c' = sqrt(log2e/2)/sigma_n, k' = (logc-L)*log2e
-    //   quantised : {mu_hi, r,  m_r = -mu_lo*r,  w }     r  = 1/(sqrt2 sigma_n)
+    // FP32 folded tables for the scoring kernels: two float4 per component, each value duplicated so that the
+    // packed FP32x2 instructions take it straight from an LDS.128; Kpad entries
+    //   continuous: {-mu_hi x2, c' x2} {-mu_lo*c' x2, k' x2}   c' = sqrt(log2e/2)/sigma_n, k' = (logc-L)*log2e
+    //   quantised : {-mu_hi x2, r' x2} {-mu_lo*r' x2, +-w x2}  r' = sqrt(log2e)/(sqrt2 sigma_n); w<0: sigma_min class
     float4 *tab[2];
     // categorical: probabilities and the log-ratio table
     double *cat_p[2];
     double *cat_score;        // log pl[c] - log pg[c]
     int32_t *cat_rank;        // dense rank of cat_score (ties share a rank)
     int32_t numeric_slot;     // index among numeric dims (-1 for categorical)
+    // quantised parameters, components whose sigma was clipped to the magic-clip floor (nearly all of them once the
+    // history is dense): Phi(b)-Phi(a) with the fixed half width h0 is one function of y = |x-mu|/(sqrt2 sigma):
+    //   erfc(y-h0) - erfc(y+h0) = 2^( -(y'-h0')^2 + R(tau) ),  y' = sqrt(log2 e) y, tau = y' * qf_tau_s - 1,
+    // R = degree-KB_QF_DEG polynomial fitted per (parameter, side) at build time (Chebyshev-node interpolation).
+    float qf_coef[2][16];
+    float qf_h0[2];           // h0' = sqrt(log2 e) * q / (2 sqrt2 sigma_min)
+    float qf_tau_s[2];        // 2 / (sqrt(log2 e) * KB_QF_YMAX)
+    float qf_hw[2];           // normalised half bin width q_n / 2 the fit assumes
 };
+#define KB_QF_DEG 12
+#define KB_QF_YMAX 7.5
 
 #define KB_TABLE_PAD 32
 
@@ -43,7 +54,8 @@ struct KbTie {
     unsigned long long key;     // f64 bits of the candidate value, ~0 = empty
     unsigned long long minidx;  // lowest global index seen with that value
 };
-#define KB_TIE_SLOTS (1u << 16)
+#define KB_TIE_SLOTS_MIN (1u << 12)
+#define KB_TIE_SLOTS_MAX (1u << 20)
 #define KB_TIE_EMPTY 0xFFFFFFFFFFFFFFFFull
 
 struct KbSelect {                // per-parameter running selection state (device)
@@ -101,11 +113,13 @@ struct kb_ctx {
     float4 *d_stage_quant = nullptr; // [n_quant][chunk]  (lb_hi, lb_lo, ub_hi, ub_lo) normalised
     double *d_scores_chunk = nullptr; // [chunk x D] dense scores (kb_tpe_scores only)
     KbSelect *d_sel = nullptr;       // [D]
-    KbTie *d_tie = nullptr;          // [n_numeric][KB_TIE_SLOTS]
+    KbTie *d_tie = nullptr;          // [n_numeric][tie_slots]
     KbWinner *d_win = nullptr;       // [D]
     KbWinner *d_win_all = nullptr;   // [world][D] (gather target)
-    float *d_tie_score = nullptr;    // [n_numeric][KB_TIE_SLOTS] FP32 score stored with each near-tie entry
-    void *d_partial = nullptr;       // [n_numeric][RS_BLOCKS] partial FP64 winners (kb_tpe_score.cu)
+    float *d_tie_score = nullptr;    // [n_numeric][tie_slots] FP32 score stored with each near-tie entry
+    unsigned int tie_slots = 0;      // slots per numeric parameter in d_tie (power of two, sized from n_cand)
+    void *d_tie_list = nullptr;      // [n_numeric][tie_slots] KbCand: compacted near ties awaiting FP64 re-scoring
+    unsigned int *d_tie_count = nullptr;  // [n_numeric]
     int *d_slot_of_dim = nullptr;    // [D] index of a parameter inside its cont / quant / cat list
     int *d_numeric_dims = nullptr;   // [n_numeric] parameter index per numeric slot
     KbWinner *h_win = nullptr;       // pinned host mirror of d_win

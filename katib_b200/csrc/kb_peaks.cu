@@ -36,6 +36,21 @@ __global__ void __launch_bounds__(PK_THREADS) peak_ffma_kernel(float *out, float
     if (s == 123.456f) out[0] = s;
 }
 
+__global__ void __launch_bounds__(PK_THREADS) peak_ffma2_kernel(float *out, float seed) {
+    float2 a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = make_float2(seed + (float)(threadIdx.x + i), seed - (float)i);
+    const float2 m = make_float2(1.000001f, 0.999999f), c = make_float2(seed, seed);
+    for (int it = 0; it < PK_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] = __ffma2_rn(a[i], m, c);  // FFMA2: two FMAs per lane per instruction
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += a[i].x + a[i].y;
+    if (s == 123.456f) out[0] = s;
+}
+
 __global__ void __launch_bounds__(PK_THREADS) peak_dfma_kernel(double *out, double seed) {
     double a[8];
 #pragma unroll
@@ -70,7 +85,7 @@ extern "C" int kb_peak_measure(kb_ctx *ctx, int which, double *out) {
     KB_CUDA(ctx, cudaEventCreate(&e1));
     void *buf = nullptr;
     const size_t bytes = (size_t)4 << 30;  // 4 GiB: far beyond the 126 MB L2
-    if (which >= 3) KB_CUDA(ctx, cudaMalloc(&buf, which == 4 ? 2 * bytes : bytes));
+    if (which == 3 || which == 4) KB_CUDA(ctx, cudaMalloc(&buf, which == 4 ? 2 * bytes : bytes));
     else KB_CUDA(ctx, cudaMalloc(&buf, 256));
     const int grid = sms * 8;
     double best = 0.0;
@@ -82,6 +97,7 @@ extern "C" int kb_peak_measure(kb_ctx *ctx, int which, double *out) {
             case 1: peak_ffma_kernel<<<grid, PK_THREADS, 0, s>>>((float *)buf, 0.5f); work = (double)grid * PK_THREADS * PK_ITERS * 16; break;
             case 2: peak_dfma_kernel<<<grid, PK_THREADS, 0, s>>>((double *)buf, 0.5); work = (double)grid * PK_THREADS * PK_ITERS * 8; break;
             case 3: peak_write_kernel<<<sms * 16, PK_THREADS, 0, s>>>((double2 *)buf, bytes / 16); work = (double)bytes; break;
+            case 5: peak_ffma2_kernel<<<grid, PK_THREADS, 0, s>>>((float *)buf, 0.5f); work = (double)grid * PK_THREADS * PK_ITERS * 16; break;
             case 4: peak_copy_kernel<<<sms * 16, PK_THREADS, 0, s>>>((const double2 *)buf, (double2 *)((char *)buf + bytes), bytes / 16); work = 2.0 * (double)bytes; break;
             default: cudaFree(buf); return kb_fail(ctx, KB_ERR_INVALID, "kb_peak_measure: which=%d", which);
         }

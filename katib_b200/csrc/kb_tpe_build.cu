@@ -219,10 +219,56 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     const double LOG2E = 1.4426950408889634;
     float4 *tab = dm.tab[side];
     const bool quant = dm.q > 0.0;
+    double dd2 = 1.0 + (double)K;
+    if (dd2 > 100.0) dd2 = 100.0;
+    const double minsigma2 = 1.0 * (high - low) / dd2;  // the magic-clip floor (same expression as above)
+    if (quant && tid == 0) {
+        // fit R(tau) = log2( erfcx(y-h) - e^{-4yh} erfcx(y+h) ) on y in [0, YMAX] by interpolation at M Chebyshev nodes
+        const int N = KB_QF_DEG, M = 40;
+        const double h = dm.q / (2.0 * sqrt(2.0) * minsigma2);
+        double cheb[KB_QF_DEG + 1];
+        for (int nn = 0; nn <= N; nn++) cheb[nn] = 0.0;
+        for (int k = 0; k < M; k++) {
+            const double th = M_PI * ((double)k + 0.5) / (double)M;
+            const double y = (cos(th) + 1.0) * (KB_QF_YMAX / 2.0);
+            const double f = log2(erfcx(y - h) - exp(-4.0 * y * h) * erfcx(y + h));
+            for (int nn = 0; nn <= N; nn++) cheb[nn] += f * cos((double)nn * th);
+        }
+        for (int nn = 0; nn <= N; nn++) cheb[nn] *= (nn == 0 ? 1.0 : 2.0) / (double)M;
+        // Chebyshev -> monomial: T0 = 1, T1 = x, T_{n+1} = 2 x T_n - T_{n-1}
+        double mono[KB_QF_DEG + 1], tp[KB_QF_DEG + 1], tc[KB_QF_DEG + 1], tn[KB_QF_DEG + 1];
+        for (int i = 0; i <= N; i++) { mono[i] = 0.0; tp[i] = 0.0; tc[i] = 0.0; }
+        tp[0] = 1.0; tc[1] = 1.0;
+        mono[0] += cheb[0];
+        for (int i = 0; i <= N; i++) mono[i] += cheb[1] * tc[i];
+        for (int nn = 2; nn <= N; nn++) {
+            for (int i = 0; i <= N; i++) tn[i] = (i > 0 ? 2.0 * tc[i - 1] : 0.0) - tp[i];
+            for (int i = 0; i <= N; i++) { mono[i] += cheb[nn] * tn[i]; tp[i] = tc[i]; tc[i] = tn[i]; }
+        }
+        for (int i = 0; i < 16; i++) dm.qf_coef[side][i] = i <= N ? (float)mono[i] : 0.f;
+        dm.qf_h0[side] = (float)(sqrt(LOG2E) * h);
+        dm.qf_tau_s[side] = (float)(2.0 / (sqrt(LOG2E) * KB_QF_YMAX));
+        dm.qf_hw[side] = (float)(0.5 * dm.q * inv_range);
+    }
+    // self-check of the fit (quantised only): the fast path is switched off (h0 <= 0) when the interpolant misses
+    // the exact bin integral by more than 1e-6 anywhere on a 3x finer grid (happens for bins much wider than sigma)
+    if (quant && tid == 0) {
+        const double h = dm.q / (2.0 * sqrt(2.0) * minsigma2);
+        double worst = 0.0;
+        for (int k = 0; k <= 128; k++) {
+            const double y = KB_QF_YMAX * (double)k / 128.0, tau = 2.0 * y / KB_QF_YMAX - 1.0;
+            double pv = (double)dm.qf_coef[side][KB_QF_DEG];
+            for (int i = KB_QF_DEG - 1; i >= 0; i--) pv = pv * tau + (double)dm.qf_coef[side][i];
+            const double exact = log2(erfcx(y - h) - exp(-4.0 * y * h) * erfcx(y + h));
+            worst = fmax(worst, fabs(exp2(pv - exact) - 1.0));
+        }
+        if (!(worst < 1e-6)) dm.qf_h0[side] = -1.f;
+    }
     for (int j = tid; j < Kpad; j += nt) {
-        float4 e;
+        float4 A, B;  // A = {-mu_hi, -mu_hi, s, s}  B = {-mu_lo*s, -mu_lo*s, t, t}
         if (j >= K) {
-            e = quant ? make_float4(0.f, 0.f, 0.f, 0.f) : make_float4(0.f, 0.f, 0.f, -INFINITY);
+            A = make_float4(0.f, 0.f, 0.f, 0.f);
+            B = quant ? make_float4(0.f, 0.f, 0.f, 0.f) : make_float4(0.f, 0.f, -INFINITY, -INFINITY);
         } else {
             double mun = (mu[j] - low) * inv_range;
             float mh = (float)mun;
@@ -231,14 +277,22 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
                 double den = sqrt(2.0) * sg[j];
                 if (den < KB_EPS) den = KB_EPS;
                 float r = (float)(sqrt(LOG2E) * (high - low) / den);  // sqrt(log2 e) / (sqrt2 sigma_n)
-                e = make_float4(mh, r, (float)(-ml * (double)r), (float)w[j]);
+                // a negative weight marks the sigma == magic-clip-floor class served by the fitted fast path
+                const float wf = (float)w[j];
+                const float ws = sg[j] == minsigma2 ? -wf : wf;
+                const float mr = (float)(-ml * (double)r);
+                A = make_float4(-mh, -mh, r, r);
+                B = make_float4(mr, mr, ws, ws);
             } else {
                 double s = sg[j] > KB_EPS ? sg[j] : KB_EPS;
                 float c = (float)(sqrt(0.5 * LOG2E) * (high - low) / s);
-                e = make_float4(mh, c, (float)(-ml * (double)c), (float)((logc[j] - L) * LOG2E));
+                const float mc = (float)(-ml * (double)c), kk = (float)((logc[j] - L) * LOG2E);
+                A = make_float4(-mh, -mh, c, c);
+                B = make_float4(mc, mc, kk, kk);
             }
         }
-        tab[j] = e;
+        tab[2 * j] = A;
+        tab[2 * j + 1] = B;
     }
 }
 
@@ -328,7 +382,7 @@ extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *v
     for (int d = 0; d < D; d++) {
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
-        else bytes += 2 * (size_t)Kcap * (4 * sizeof(double) + sizeof(float4));
+        else bytes += 2 * (size_t)Kcap * (4 * sizeof(double) + 2 * sizeof(float4));
     }
     if (bytes > ctx->tabmem_bytes) {
         cudaFree(ctx->d_tabmem); ctx->d_tabmem = nullptr;
@@ -346,7 +400,7 @@ extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *v
             k.cat_rank = (int32_t *)p; p += c * sizeof(double);
         } else {
             for (int side = 0; side < 2; side++) {
-                k.tab[side] = (float4 *)p; p += (size_t)Kcap * sizeof(float4);
+                k.tab[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
                 k.mu[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.sigma[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);

@@ -26,7 +26,10 @@
 #include "kb_internal.cuh"
 
 #define KB_EPS 1e-12
-#define KB_MARGIN_REL 3e-5f
+// Admission margin of the near-tie table, relative to max(1, |score|): several times the largest FP32
+// error measured against the FP64 oracle (continuous 7e-7, quantised 2e-6; tests/test_gpu_tpe.py prints them).
+#define KB_MARGIN_CONT 4e-6f
+#define KB_MARGIN_QUANT 1.5e-5f
 
 // ---------------------------------------------------------------------------------------------------------
 // mbarrier / TMA bulk-copy helpers (sm_90+; SASS: UBLKCP + SYNCS)
@@ -108,10 +111,11 @@ tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict
                     if (q > 0.0) {
                         double ub = x + q / 2.0; ub = ub > hi ? hi : ub;
                         double lb = x - q / 2.0; lb = lb < lo ? lo : lb;
-                        double un = (ub - lo) * inv, ln = (lb - lo) * inv;
-                        float uh = (float)un, lh = (float)ln;
-                        stage_quant[(size_t)slot * chunk_cap + row0 + r] =
-                            make_float4(lh, (float)(ln - (double)lh), uh, (float)(un - (double)uh));
+                        // bin midpoint (hi, lo) and half width, normalised; w = 1 when the bin is a full quantum
+                        double mn = (0.5 * (ub + lb) - lo) * inv, hn = 0.5 * (ub - lb) * inv;
+                        float mh = (float)mn, hwf = (float)hn;
+                        float regular = fabs(hn - 0.5 * q * inv) <= 1e-9 * (q * inv) ? 1.f : 0.f;
+                        stage_quant[(size_t)slot * chunk_cap + row0 + r] = make_float4(mh, (float)(mn - (double)mh), hwf, regular);
                     } else {
                         double xn = (x - lo) * inv;
                         float xh = (float)xn;
@@ -127,18 +131,18 @@ tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict
 // ---------------------------------------------------------------------------------------------------------
 // near-tie table insert
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void tie_insert(KbTie *tab, float *tab_score, KbSelect *sl, unsigned long long key,
-                                           unsigned long long gidx, float score) {
+__device__ __forceinline__ void tie_insert(KbTie *tab, float *tab_score, unsigned int slots, KbSelect *sl,
+                                           unsigned long long key, unsigned long long gidx, float score) {
     unsigned long long h = key * 0x9E3779B97F4A7C15ull;
-    unsigned int s = (unsigned int)(h >> 40) & (KB_TIE_SLOTS - 1);
-    for (unsigned int probe = 0; probe < KB_TIE_SLOTS / 2; probe++) {
+    unsigned int s = (unsigned int)(h >> 40) & (slots - 1);
+    for (unsigned int probe = 0; probe < 4096u && probe < slots; probe++) {
         unsigned long long prev = atomicCAS(&tab[s].key, KB_TIE_EMPTY, key);
         if (prev == KB_TIE_EMPTY || prev == key) {
             atomicMin(&tab[s].minidx, gidx);
             tab_score[s] = score;  // every writer of this key stores the same bits
             return;
         }
-        s = (s + 1) & (KB_TIE_SLOTS - 1);
+        s = (s + 1) & (slots - 1);
     }
     atomicExch(&sl->overflow, 1u);
 }
@@ -147,7 +151,7 @@ __device__ __forceinline__ void tie_insert(KbTie *tab, float *tab_score, KbSelec
 template <int R, int THREADS>
 __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_base, int n, long long idx_base, int d,
                                                int D, int numeric_slot, KbSelect *sel, KbTie *tie, float *tie_score,
-                                               const double *__restrict__ cand_raw) {
+                                               unsigned int slots, float margin, const double *__restrict__ cand_raw) {
     __shared__ float s_wmax[THREADS / 32];
     __shared__ float s_thr;
     float best = -INFINITY;
@@ -165,31 +169,36 @@ __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_ba
         unsigned int mine = kb_f32_orderable(b);
         unsigned int old = atomicMax(&sel[d].gmax_bits, mine);
         float g = kb_f32_from_orderable(old > mine ? old : mine);
-        float thr = g - KB_MARGIN_REL * fmaxf(1.0f, fabsf(g));
+        float thr = g - margin * fmaxf(1.0f, fabsf(g));
         s_thr = b >= thr ? thr : INFINITY;  // block has nothing near the maximum: skip the scan
     }
     __syncthreads();
     const float thr = s_thr;
     if (thr == INFINITY) return;
-    KbTie *tab = tie + (size_t)numeric_slot * KB_TIE_SLOTS;
-    float *tsc = tie_score + (size_t)numeric_slot * KB_TIE_SLOTS;
+    KbTie *tab = tie + (size_t)numeric_slot * slots;
+    float *tsc = tie_score + (size_t)numeric_slot * slots;
 #pragma unroll
     for (int r = 0; r < R; r++) {
         int i = tile_base + r * THREADS + threadIdx.x;
         if (i < n && sc[r] >= thr) {
             unsigned long long key = (unsigned long long)__double_as_longlong(cand_raw[(size_t)i * D + d]);
-            tie_insert(tab, tsc, &sel[d], key, (unsigned long long)(idx_base + i), sc[r]);
+            tie_insert(tab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + i), sc[r]);
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // continuous parameters (q = 0): log-sum-exp over the below and above mixtures
+//
+// Table entry = two float4, pre-duplicated so that the packed FP32x2 instructions of sm_100 (FADD2 / FFMA2:
+// one issue slot for two candidates) can take them as they come out of one LDS.128 each:
+//   A = {-mu_hi, -mu_hi, c', c'}   B = {-mu_lo*c', -mu_lo*c', k', k'}
+// Per pair of (candidate, component) evaluations: 2 FADD2 + 2 FFMA2 + 2 MUFU.EX2 + 1 FADD2.
 // ---------------------------------------------------------------------------------------------------------
 #define SC_THREADS 256
 #define SC_R 8
 #define SC_TILE (SC_THREADS * SC_R)
-#define SC_CHUNK 1024  // components per shared-memory stage (16 KB)
+#define SC_CHUNK 512   // components per shared-memory stage (2 float4 each: 16 KB)
 #define SC_STAGES 2
 #define SC_GROUP 32    // components per FP32 partial sum
 
@@ -197,17 +206,25 @@ __device__ __forceinline__ void table_stream_issue(const KbDim &dm, int chunk, i
     const int side = chunk < nchunk0 ? 0 : 1;
     const int c = side == 0 ? chunk : chunk - nchunk0;
     const int cnt = min(SC_CHUNK, dm.Kpad[side] - c * SC_CHUNK);
-    const uint32_t bytes = (uint32_t)cnt * (uint32_t)sizeof(float4);
+    const uint32_t bytes = (uint32_t)cnt * 2u * (uint32_t)sizeof(float4);
     mbar_expect_tx(bar, bytes);
-    tma_bulk_g2s(dst, dm.tab[side] + (size_t)c * SC_CHUNK, bytes, bar);
+    tma_bulk_g2s(dst, dm.tab[side] + (size_t)c * SC_CHUNK * 2, bytes, bar);
+}
+
+// (hi, lo) += a with the rounding error of the add recovered (TwoSum): keeps ~48 bits without touching FP64
+__device__ __forceinline__ void two_sum_acc(float &hi, float &lo, float a) {
+    const float s = hi + a;
+    const float bb = s - hi;
+    lo += (hi - (s - bb)) + (a - bb);
+    hi = s;
 }
 
 __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                       const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
-                      KbSelect *sel, KbTie *tie, float *tie_score, const double *__restrict__ cand_raw,
-                      double *__restrict__ scores_out) {
-    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK];
+                      KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
+                      const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
+    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     const int slot = blockIdx.y;
     const int d = cont_dims[slot];
@@ -224,16 +241,17 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
     if (threadIdx.x == 0)
         for (int c = 0; c < SC_STAGES && c < nchunks; c++) table_stream_issue(dm, c, nchunk0, s_tab[c], &s_bar[c]);
 
-    float xh[SC_R], xl[SC_R];
+    float2 xh[SC_R / 2], xl[SC_R / 2];  // candidate pairs (r, r+1)
 #pragma unroll
     for (int r = 0; r < SC_R; r++) {
         int i = tile_base + r * SC_THREADS + threadIdx.x;
         float2 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float2(0.5f, 0.f);
-        xh[r] = v.x; xl[r] = v.y;
+        if (r & 1) { xh[r / 2].y = v.x; xl[r / 2].y = v.y; } else { xh[r / 2].x = v.x; xl[r / 2].x = v.y; }
     }
-    double S[SC_R], logS0[SC_R];
+    float Shi[SC_R], Slo[SC_R];
+    double logS0[SC_R];
 #pragma unroll
-    for (int r = 0; r < SC_R; r++) S[r] = 0.0;
+    for (int r = 0; r < SC_R; r++) { Shi[r] = 0.f; Slo[r] = 0.f; }
 
     for (int c = 0; c < nchunks; c++) {
         const int st = c % SC_STAGES;
@@ -243,47 +261,63 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
         mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
         const float4 *tab = s_tab[st];
         for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
-            float a32[SC_R];
+            float2 a32[SC_R / 2];
 #pragma unroll
-            for (int r = 0; r < SC_R; r++) a32[r] = 0.f;
+            for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
 #pragma unroll 4
             for (int j = 0; j < SC_GROUP; j++) {
-                const float4 e = tab[j0 + j];  // {mu_hi, c', -mu_lo*c', k'}: one broadcast LDS.128
+                const float4 A = tab[2 * (j0 + j)], B = tab[2 * (j0 + j) + 1];  // two broadcast LDS.128
+                const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
+                const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
 #pragma unroll
-                for (int r = 0; r < SC_R; r++) {
-                    float u = xh[r] - e.x;
-                    u += xl[r];
-                    float t = fmaf(u, e.y, e.z);
-                    a32[r] += kb_ex2(fmaf(-t, t, e.w));
+                for (int p = 0; p < SC_R / 2; p++) {
+                    float2 u = __fadd2_rn(xh[p], nmu);
+                    u = __fadd2_rn(u, xl[p]);
+                    const float2 t = __ffma2_rn(u, cs, ms);
+                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
                 }
             }
 #pragma unroll
-            for (int r = 0; r < SC_R; r++) S[r] += (double)a32[r];
+            for (int p = 0; p < SC_R / 2; p++) {
+                two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
+                two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
+            }
         }
         __syncthreads();  // every thread is done with stage st
         if (threadIdx.x == 0 && c + SC_STAGES < nchunks)
             table_stream_issue(dm, c + SC_STAGES, nchunk0, s_tab[st], &s_bar[st]);
         if (c == nchunk0 - 1) {
 #pragma unroll
-            for (int r = 0; r < SC_R; r++) { logS0[r] = log(S[r]) + dm.L[0]; S[r] = 0.0; }
+            for (int r = 0; r < SC_R; r++) {
+                logS0[r] = log((double)Shi[r] + (double)Slo[r]) + dm.L[0];
+                Shi[r] = 0.f; Slo[r] = 0.f;
+            }
         }
     }
     float sc[SC_R];
 #pragma unroll
     for (int r = 0; r < SC_R; r++) {
-        double s64 = logS0[r] - (log(S[r]) + dm.L[1]);
+        double s64 = logS0[r] - (log((double)Shi[r] + (double)Slo[r]) + dm.L[1]);
         sc[r] = (float)s64;
         int i = tile_base + r * SC_THREADS + threadIdx.x;
         if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
     }
-    if (sel) select_publish<SC_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, cand_raw);
+    if (sel) select_publish<SC_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
+                                                  KB_MARGIN_CONT, cand_raw);
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// quantised parameters (q > 0): sum_j w_j (Phi(ub) - Phi(lb)) per side, written as erfc differences so that
-// the tails keep relative accuracy in FP32
+// quantised parameters (q > 0): p(x) = sum_j w_j (Phi(ub) - Phi(lb)) per side.
+//
+// Table entry (same duplicated layout): A = {-mu_hi, -mu_hi, r', r'}  B = {-mu_lo*r', -mu_lo*r', +-w, +-w},
+// r' = sqrt(log2 e)/(sqrt2 sigma_n).  Three warp-uniform component classes:
+//   w < 0  sigma sits on the magic-clip floor (nearly every component of a dense history): the bin integral is one
+//          function of y = |x-mu| r', fitted at build time: 2^(-(y-h0)^2 + R12(tau)); packed FP32x2, 1 MUFU each
+//   narrow bin (b-a <= 0.2): Taylor/Hermite series about the bin midpoint (erfc differences would cancel)
+//   else   erfc(a) - erfc(b) with a hand-fitted erfcx (1 MUFU.RCP + 1 MUFU.EX2 each), mirrored onto y >= 0
 // ---------------------------------------------------------------------------------------------------------
-#define SQ_R 4
+#define SQ_R 8
 #define SQ_TILE (SC_THREADS * SQ_R)
 #define LN2F 0.6931471806f
 #define KINVF 0.8325546112f           // 1/sqrt(log2 e)
@@ -308,12 +342,12 @@ __device__ __forceinline__ float erfc_pos_scaled(float xs) {
     return (p * t) * kb_ex2(-xs * xs);
 }
 
-__global__ void __launch_bounds__(SC_THREADS, 3)
+__global__ void __launch_bounds__(SC_THREADS, 2)
 tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
                        const float4 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
-                       KbSelect *sel, KbTie *tie, float *tie_score, const double *__restrict__ cand_raw,
-                       double *__restrict__ scores_out) {
-    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK];
+                       KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
+                       const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
+    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     const int slot = blockIdx.y;
     const int d = quant_dims[slot];
@@ -330,17 +364,24 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
     if (threadIdx.x == 0)
         for (int c = 0; c < SC_STAGES && c < nchunks; c++) table_stream_issue(dm, c, nchunk0, s_tab[c], &s_bar[c]);
 
-    float lh[SQ_R], ll[SQ_R], uh[SQ_R], ul[SQ_R];
+    float2 xm[SQ_R / 2], xl[SQ_R / 2], hw[SQ_R / 2];
+    bool all_regular = true;
 #pragma unroll
     for (int r = 0; r < SQ_R; r++) {
         int i = tile_base + r * SC_THREADS + threadIdx.x;
-        float4 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float4(0.4f, 0.f, 0.6f, 0.f);
-        lh[r] = v.x; ll[r] = v.y; uh[r] = v.z; ul[r] = v.w;
+        float4 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float4(0.5f, 0.f, dm.qf_hw[0], 1.f);
+        if (r & 1) { xm[r / 2].y = v.x; xl[r / 2].y = v.y; hw[r / 2].y = v.z; }
+        else { xm[r / 2].x = v.x; xl[r / 2].x = v.y; hw[r / 2].x = v.z; }
+        all_regular = all_regular && v.w != 0.f;
     }
-    double S[SQ_R], P0[SQ_R];
+    float Shi[SQ_R], Slo[SQ_R];
+    double P0[SQ_R];
 #pragma unroll
-    for (int r = 0; r < SQ_R; r++) S[r] = 0.0;
+    for (int r = 0; r < SQ_R; r++) { Shi[r] = 0.f; Slo[r] = 0.f; }
     const float qn = (float)(dm.q / (dm.hi - dm.lo));
+    float2 qc[KB_QF_DEG + 1];
+    float2 qnh0 = make_float2(0.f, 0.f), qts = make_float2(0.f, 0.f);
+    bool fast_ok = false;
 
     for (int c = 0; c < nchunks; c++) {
         const int st = c % SC_STAGES;
@@ -349,22 +390,43 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
         const int cnt = min(SC_CHUNK, dm.Kpad[side] - cc * SC_CHUNK);
         mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
         const float4 *tab = s_tab[st];
-        for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
-            float a32[SQ_R];
+        if (cc == 0) {  // per-side constants of the fitted class
 #pragma unroll
-            for (int r = 0; r < SQ_R; r++) a32[r] = 0.f;
+            for (int i = 0; i <= KB_QF_DEG; i++) { const float v = dm.qf_coef[side][i]; qc[i] = make_float2(v, v); }
+            qnh0 = make_float2(-dm.qf_h0[side], -dm.qf_h0[side]);
+            qts = make_float2(dm.qf_tau_s[side], dm.qf_tau_s[side]);
+            fast_ok = all_regular && dm.qf_h0[side] > 0.f;
+        }
+        for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
+            float2 a32[SQ_R / 2];
+#pragma unroll
+            for (int p = 0; p < SQ_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
 #pragma unroll 2
             for (int j = 0; j < SC_GROUP; j++) {
-                const float4 e = tab[j0 + j];  // {mu_hi, r', -mu_lo*r', w},  r' = sqrt(log2 e) / (sqrt2 sigma_n)
-                // erfc arguments scaled by sqrt(log2 e): a' = k a, b' = k b, so that e^{-a^2} = 2^{-a'^2}
-                if (e.y * qn < QUANT_WIDE_THR) {
-                    // bin narrow against sigma (b - a <= 0.2): erfc(a) - erfc(b) would cancel, so integrate the
-                    // Gaussian over the bin by its Taylor series about the midpoint (Hermite terms to h^6)
+                const float4 A = tab[2 * (j0 + j)], B = tab[2 * (j0 + j) + 1];
+                const float2 nmu = make_float2(A.x, A.y), rs = make_float2(A.z, A.w), ms = make_float2(B.x, B.y);
+                const float wj = fabsf(B.z);
+                if (B.z < 0.f && fast_ok) {
+                    const float2 w2 = make_float2(wj, wj);
+#pragma unroll
+                    for (int p = 0; p < SQ_R / 2; p++) {
+                        const float2 m = __ffma2_rn(__fadd2_rn(__fadd2_rn(xm[p], nmu), xl[p]), rs, ms);
+                        const float2 y = make_float2(fabsf(m.x), fabsf(m.y));
+                        float2 tau = __ffma2_rn(y, qts, make_float2(-1.f, -1.f));
+                        tau = make_float2(fminf(tau.x, 1.f), fminf(tau.y, 1.f));
+                        const float2 z = __fadd2_rn(y, qnh0);
+                        float2 pp = qc[KB_QF_DEG];
+#pragma unroll
+                        for (int i = KB_QF_DEG - 1; i >= 0; i--) pp = __ffma2_rn(pp, tau, qc[i]);
+                        const float2 e = __ffma2_rn(make_float2(-z.x, -z.y), z, pp);
+                        a32[p] = __ffma2_rn(w2, make_float2(kb_ex2(e.x), kb_ex2(e.y)), a32[p]);
+                    }
+                } else if (A.z * qn < QUANT_WIDE_THR) {
 #pragma unroll
                     for (int r = 0; r < SQ_R; r++) {
-                        const float a = fmaf((lh[r] - e.x) + ll[r], e.y, e.z);
-                        const float b = fmaf((uh[r] - e.x) + ul[r], e.y, e.z);
-                        const float m = 0.5f * (a + b), h = 0.5f * (b - a);
+                        const float xmr = (r & 1) ? xm[r / 2].y : xm[r / 2].x, xlr = (r & 1) ? xl[r / 2].y : xl[r / 2].x;
+                        const float hwr = (r & 1) ? hw[r / 2].y : hw[r / 2].x;
+                        const float m = fmaf((xmr + A.x) + xlr, A.z, B.x), h = hwr * A.z;
                         const float mm = m * m;
                         const float u = mm * LN2F, v = (h * h) * LN2F;
                         const float c1 = fmaf(u, 0.6666666667f, -0.3333333333f);
@@ -372,51 +434,58 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
                         const float c3 = fmaf(fmaf(fmaf(u, 0.0126984127f, -0.0952380952f), u, 0.1428571429f), u, -0.0238095238f);
                         const float S = fmaf(fmaf(fmaf(c3, v, c2), v, c1), v, 1.0f);
                         const float d2 = (h * (2.2567583342f * KINVF)) * S * kb_ex2(-mm);  // (4/sqrt(pi)) h S e^{-m^2}
-                        a32[r] = fmaf(e.w, d2, a32[r]);
+                        if (r & 1) a32[r / 2].y = fmaf(wj, d2, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, d2, a32[r / 2].x);
                     }
                 } else {
 #pragma unroll
                     for (int r = 0; r < SQ_R; r++) {
-                        const float a = fmaf((lh[r] - e.x) + ll[r], e.y, e.z);
-                        const float b = fmaf((uh[r] - e.x) + ul[r], e.y, e.z);
-                        // Phi(b)-Phi(a) = (erfc(a)-erfc(b))/2; mirror so that b >= |a| (erfc small, relative accuracy kept)
-                        const bool flip = a + b < 0.f;
-                        const float a2 = flip ? -b : a, b2 = flip ? -a : b;
+                        const float xmr = (r & 1) ? xm[r / 2].y : xm[r / 2].x, xlr = (r & 1) ? xl[r / 2].y : xl[r / 2].x;
+                        const float hwr = (r & 1) ? hw[r / 2].y : hw[r / 2].x;
+                        const float ma = fabsf(fmaf((xmr + A.x) + xlr, A.z, B.x)), h = hwr * A.z;
+                        // Phi(b)-Phi(a) = (erfc(a)-erfc(b))/2 with a = m-h, b = m+h, mirrored so that b >= |a|
+                        const float a2 = ma - h, b2 = ma + h;
                         const float ea = erfc_pos_scaled(fabsf(a2)), eb = erfc_pos_scaled(b2);
                         const float ea2 = a2 < 0.f ? 2.0f - ea : ea;
-                        a32[r] = fmaf(e.w, ea2 - eb, a32[r]);
+                        if (r & 1) a32[r / 2].y = fmaf(wj, ea2 - eb, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, ea2 - eb, a32[r / 2].x);
                     }
                 }
             }
 #pragma unroll
-            for (int r = 0; r < SQ_R; r++) S[r] += (double)a32[r];
+            for (int p = 0; p < SQ_R / 2; p++) {
+                two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
+                two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
+            }
         }
         __syncthreads();
         if (threadIdx.x == 0 && c + SC_STAGES < nchunks)
             table_stream_issue(dm, c + SC_STAGES, nchunk0, s_tab[st], &s_bar[st]);
         if (c == nchunk0 - 1) {
 #pragma unroll
-            for (int r = 0; r < SQ_R; r++) { P0[r] = log(0.5 * S[r] + KB_EPS) - log(dm.p_accept[0] + KB_EPS); S[r] = 0.0; }
+            for (int r = 0; r < SQ_R; r++) {
+                P0[r] = log(0.5 * ((double)Shi[r] + (double)Slo[r]) + KB_EPS) - log(dm.p_accept[0] + KB_EPS);
+                Shi[r] = 0.f; Slo[r] = 0.f;
+            }
         }
     }
     float sc[SQ_R];
 #pragma unroll
     for (int r = 0; r < SQ_R; r++) {
-        double s64 = P0[r] - (log(0.5 * S[r] + KB_EPS) - log(dm.p_accept[1] + KB_EPS));
+        double s64 = P0[r] - (log(0.5 * ((double)Shi[r] + (double)Slo[r]) + KB_EPS) - log(dm.p_accept[1] + KB_EPS));
         sc[r] = (float)s64;
         int i = tile_base + r * SC_THREADS + threadIdx.x;
         if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
     }
-    if (sel) select_publish<SQ_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, cand_raw);
+    if (sel) select_publish<SQ_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
+                                                  KB_MARGIN_QUANT, cand_raw);
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // FP64 re-scoring of the near ties (oracle formula order: max, sum of exp, log) and the final pick
 // ---------------------------------------------------------------------------------------------------------
 #define RS_THREADS 256
-#define RS_BLOCKS 8
+#define RS_GRID_X 64
 
-struct KbPartial { double score; unsigned long long idx; double value; };
+struct KbCand { double x; unsigned long long idx; double score; };
 
 __device__ double rescore_value(const KbDim &dm, double x, int lane) {
     double out[2];
@@ -457,67 +526,88 @@ __device__ double rescore_value(const KbDim &dm, double x, int lane) {
     return out[0] - out[1];
 }
 
+// table -> dense list of the entries still within the margin of the FINAL maximum
 __global__ void __launch_bounds__(RS_THREADS)
-tpe_rescore_kernel(const KbDim *__restrict__ dims, const int *__restrict__ numeric_dims, const KbSelect *__restrict__ sel,
-                   const KbTie *__restrict__ tie, const float *__restrict__ tie_score, KbPartial *partial) {
-    __shared__ KbPartial s_best[RS_THREADS / 32];
-    const int slot = blockIdx.x, d = numeric_dims[slot];
-    const KbDim &dm = dims[d];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+tpe_compact_kernel(const KbDim *__restrict__ dims, const int *__restrict__ numeric_dims, const KbSelect *__restrict__ sel,
+                   const KbTie *__restrict__ tie, const float *__restrict__ tie_score, unsigned int slots, KbCand *list,
+                   unsigned int *count) {
+    const int slot = blockIdx.y, d = numeric_dims[slot];
     const float g = kb_f32_from_orderable(sel[d].gmax_bits);
-    const float thr = g - KB_MARGIN_REL * fmaxf(1.0f, fabsf(g));
-    const KbTie *tab = tie + (size_t)slot * KB_TIE_SLOTS;
-    const float *tsc = tie_score + (size_t)slot * KB_TIE_SLOTS;
-    KbPartial best = {-INFINITY, ~0ull, 0.0};
-    const int wglobal = blockIdx.y * (RS_THREADS / 32) + warp, wtotal = RS_BLOCKS * (RS_THREADS / 32);
-    for (unsigned int s = wglobal; s < KB_TIE_SLOTS; s += wtotal) {
+    const float margin = dims[d].q > 0.0 ? KB_MARGIN_QUANT : KB_MARGIN_CONT;
+    const float thr = g - margin * fmaxf(1.0f, fabsf(g));
+    const KbTie *tab = tie + (size_t)slot * slots;
+    const float *tsc = tie_score + (size_t)slot * slots;
+    for (unsigned int s = blockIdx.x * blockDim.x + threadIdx.x; s < slots; s += gridDim.x * blockDim.x) {
         const unsigned long long key = tab[s].key;
-        if (key == KB_TIE_EMPTY || !(tsc[s] >= thr)) continue;  // warp-uniform
-        const double x = __longlong_as_double((long long)key);
-        const double sc = rescore_value(dm, x, lane);
-        const unsigned long long idx = tab[s].minidx;
-        if (sc > best.score || (sc == best.score && idx < best.idx)) { best.score = sc; best.idx = idx; best.value = x; }
-    }
-    if (lane == 0) s_best[warp] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        for (int w = 1; w < RS_THREADS / 32; w++) {
-            KbPartial o = s_best[w];
-            if (o.score > best.score || (o.score == best.score && o.idx < best.idx)) best = o;
-        }
-        partial[(size_t)slot * RS_BLOCKS + blockIdx.y] = best;
+        if (key == KB_TIE_EMPTY || !(tsc[s] >= thr)) continue;
+        const unsigned int pos = atomicAdd(&count[slot], 1u);
+        KbCand c = {__longlong_as_double((long long)key), tab[s].minidx, 0.0};
+        list[(size_t)slot * slots + pos] = c;
     }
 }
 
-__global__ void tpe_pick_kernel(const KbDim *__restrict__ dims, int D, const KbSelect *__restrict__ sel,
-                                const KbPartial *__restrict__ partial, KbWinner *win, long long idx_base) {
-    const int d = blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= D) return;
+// one warp per listed value: FP64 score in the oracle's formula order
+__global__ void __launch_bounds__(RS_THREADS)
+tpe_rescore_kernel(const KbDim *__restrict__ dims, const int *__restrict__ numeric_dims, unsigned int slots, KbCand *list,
+                   const unsigned int *__restrict__ count) {
+    const int slot = blockIdx.y, d = numeric_dims[slot];
+    const KbDim &dm = dims[d];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned int n = count[slot];
+    KbCand *l = list + (size_t)slot * slots;
+    for (unsigned int e = blockIdx.x * (RS_THREADS / 32) + warp; e < n; e += gridDim.x * (RS_THREADS / 32)) {
+        const double sc = rescore_value(dm, l[e].x, lane);
+        if (lane == 0) l[e].score = sc;
+    }
+}
+
+// one CTA per parameter: best listed value (score desc, index asc); categorical winners decode their packed key
+__global__ void __launch_bounds__(RS_THREADS)
+tpe_pick_kernel(const KbDim *__restrict__ dims, const KbSelect *__restrict__ sel, unsigned int slots,
+                const KbCand *__restrict__ list, const unsigned int *__restrict__ count, KbWinner *win, long long idx_base) {
+    __shared__ KbCand s_best[RS_THREADS];
+    const int d = blockIdx.x;
     const KbDim &dm = dims[d];
     KbWinner w;
     if (dm.kind == KB_CATEGORICAL) {
+        if (threadIdx.x != 0) return;
         const unsigned long long key = sel[d].cat_best;
         const int c = (int)(key & 0xFFFull);
         const unsigned int local = ~(unsigned int)((key >> 12) & 0xFFFFFFFFull);
         w.score = key ? dm.cat_score[c] : -INFINITY;
         w.index = key ? idx_base + (long long)local : -1;
         w.value = (double)c;
-    } else {
-        KbPartial best = {-INFINITY, ~0ull, 0.0};
-        for (int b = 0; b < RS_BLOCKS; b++) {
-            KbPartial o = partial[(size_t)dm.numeric_slot * RS_BLOCKS + b];
-            if (o.score > best.score || (o.score == best.score && o.idx < best.idx)) best = o;
+        win[d] = w;
+        return;
+    }
+    const KbCand *l = list + (size_t)dm.numeric_slot * slots;
+    const unsigned int n = count[dm.numeric_slot];
+    KbCand best = {0.0, ~0ull, -INFINITY};
+    for (unsigned int e = threadIdx.x; e < n; e += RS_THREADS) {
+        KbCand o = l[e];
+        if (o.score > best.score || (o.score == best.score && o.idx < best.idx)) best = o;
+    }
+    s_best[threadIdx.x] = best;
+    __syncthreads();
+    for (int off = RS_THREADS / 2; off > 0; off >>= 1) {
+        if (threadIdx.x < off) {
+            KbCand o = s_best[threadIdx.x + off], b = s_best[threadIdx.x];
+            if (o.score > b.score || (o.score == b.score && o.idx < b.idx)) s_best[threadIdx.x] = o;
         }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        best = s_best[0];
         w.score = best.score;
         w.index = best.idx == ~0ull ? -1 : (long long)best.idx;
-        double v = best.value;
+        double v = best.x;
         if (dm.kind == KB_DISCRETE) {  // sampleDiscreteUniform: shift back and clamp
             v = v + dm.shift;
             v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         }
         w.value = v;
+        win[d] = w;
     }
-    win[d] = w;
 }
 
 // pick the best of `world` gathered winner rows (score desc, index asc)
@@ -546,9 +636,9 @@ int kb_tpe_free(kb_ctx *ctx) {
     ctx->d_stage_cont = nullptr; ctx->d_stage_quant = nullptr; ctx->d_scores_chunk = nullptr;
     ctx->d_sel = nullptr; ctx->d_tie = nullptr; ctx->d_win = nullptr; ctx->d_win_all = nullptr;
     ctx->chunk_cap = 0;
-    cudaFree(ctx->d_tie_score); cudaFree(ctx->d_partial); cudaFree(ctx->d_slot_of_dim); cudaFree(ctx->d_numeric_dims);
+    cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list); cudaFree(ctx->d_tie_count); cudaFree(ctx->d_slot_of_dim); cudaFree(ctx->d_numeric_dims);
     if (ctx->h_win) cudaFreeHost(ctx->h_win);
-    ctx->d_tie_score = nullptr; ctx->d_partial = nullptr; ctx->d_slot_of_dim = nullptr; ctx->d_numeric_dims = nullptr;
+    ctx->d_tie_score = nullptr; ctx->d_tie_list = nullptr; ctx->d_tie_count = nullptr; ctx->tie_slots = 0; ctx->d_slot_of_dim = nullptr; ctx->d_numeric_dims = nullptr;
     ctx->h_win = nullptr;
     return KB_OK;
 }
@@ -556,7 +646,7 @@ int kb_tpe_free(kb_ctx *ctx) {
 static const int64_t KB_CHUNK_ROWS = 1 << 20;
 
 // size the per-chunk scratch for `rows` candidates per chunk
-static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, bool need_landing, bool need_scores) {
+static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool need_landing, bool need_scores) {
     kb_ctx *sc = ctx;
     const int D = ctx->D;
     if (!ctx->d_sel) {
@@ -564,9 +654,7 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, bool need_landing, bool
         KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)D));
         KB_CUDA(ctx, cudaMalloc(&ctx->d_win_all, sizeof(KbWinner) * (size_t)D * 64));
         const size_t slots = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
-        KB_CUDA(ctx, cudaMalloc(&ctx->d_tie, sizeof(KbTie) * slots * KB_TIE_SLOTS));
-        KB_CUDA(ctx, cudaMalloc(&sc->d_tie_score, sizeof(float) * slots * KB_TIE_SLOTS));
-        KB_CUDA(ctx, cudaMalloc(&sc->d_partial, sizeof(KbPartial) * slots * RS_BLOCKS));
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_tie_count, sizeof(unsigned int) * slots));
         KB_CUDA(ctx, cudaMallocHost(&sc->h_win, sizeof(KbWinner) * (size_t)D));
         std::vector<int> slot_of((size_t)D, 0), numeric(slots, 0);
         for (int i = 0; i < ctx->n_cont; i++) slot_of[(size_t)ctx->cont_dims[(size_t)i]] = i;
@@ -577,6 +665,19 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, bool need_landing, bool
         KB_CUDA(ctx, cudaMalloc(&sc->d_numeric_dims, sizeof(int) * slots));
         KB_CUDA(ctx, cudaMemcpy(sc->d_slot_of_dim, slot_of.data(), sizeof(int) * (size_t)D, cudaMemcpyHostToDevice));
         KB_CUDA(ctx, cudaMemcpy(sc->d_numeric_dims, numeric.data(), sizeof(int) * slots, cudaMemcpyHostToDevice));
+    }
+    {   // near-tie table: one slot per 32 candidates, within [2^12, 2^20] per numeric parameter
+        unsigned int want = KB_TIE_SLOTS_MIN;
+        while (want < KB_TIE_SLOTS_MAX && (int64_t)want * 32 < n_cand) want <<= 1;
+        if (want > ctx->tie_slots) {
+            const size_t nn = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
+            cudaFree(ctx->d_tie); cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list);
+            ctx->d_tie = nullptr; ctx->d_tie_score = nullptr; ctx->d_tie_list = nullptr; ctx->tie_slots = 0;
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_tie, sizeof(KbTie) * nn * want));
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_tie_score, sizeof(float) * nn * want));
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_tie_list, sizeof(KbCand) * nn * want));
+            ctx->tie_slots = want;
+        }
     }
     if (rows > ctx->chunk_cap) {
         cudaFree(ctx->d_stage_cont); cudaFree(ctx->d_stage_quant);
@@ -611,14 +712,14 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
         KbProf pf(ctx, 1, s);
         tpe_score_cont_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont, ctx->chunk_cap, n,
-                                                          idx_base, D, sel, ctx->d_tie, sc->d_tie_score, d_cand, d_scores);
+                                                          idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
     }
     if (ctx->n_quant > 0) {
         dim3 grid((unsigned)((n + SQ_TILE - 1) / SQ_TILE), (unsigned)ctx->n_quant);
         KbProf pf(ctx, 2, s);
         tpe_score_quant_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant, ctx->chunk_cap,
-                                                           n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, d_cand, d_scores);
+                                                           n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
     }
     return KB_OK;
@@ -627,7 +728,8 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
 static int tpe_reset_selection(kb_ctx *ctx, cudaStream_t s) {
     const size_t slots = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
     KB_CUDA(ctx, cudaMemsetAsync(ctx->d_sel, 0, sizeof(KbSelect) * (size_t)ctx->D, s));
-    KB_CUDA(ctx, cudaMemsetAsync(ctx->d_tie, 0xFF, sizeof(KbTie) * slots * KB_TIE_SLOTS, s));
+    KB_CUDA(ctx, cudaMemsetAsync(ctx->d_tie, 0xFF, sizeof(KbTie) * slots * ctx->tie_slots, s));
+    KB_CUDA(ctx, cudaMemsetAsync(ctx->d_tie_count, 0, sizeof(unsigned int) * slots, s));
     return KB_OK;
 }
 
@@ -635,15 +737,22 @@ static int tpe_finish_selection(kb_ctx *ctx, long long idx_base, int64_t *out_in
                                 cudaStream_t s) {
     kb_ctx *sc = ctx;
     const int D = ctx->D;
-    KbProf *pf3 = new KbProf(ctx, 3, s);
-    if (ctx->n_numeric > 0) {
-        tpe_rescore_kernel<<<dim3((unsigned)ctx->n_numeric, RS_BLOCKS), RS_THREADS, 0, s>>>(
-            ctx->d_dims, sc->d_numeric_dims, ctx->d_sel, ctx->d_tie, sc->d_tie_score, (KbPartial *)sc->d_partial);
+    {
+        KbProf pf(ctx, 3, s);
+        if (ctx->n_numeric > 0) {
+            const unsigned int slots = ctx->tie_slots;
+            KbCand *list = (KbCand *)ctx->d_tie_list;
+            tpe_compact_kernel<<<dim3((slots + RS_THREADS * 8 - 1) / (RS_THREADS * 8), (unsigned)ctx->n_numeric), RS_THREADS, 0, s>>>(
+                ctx->d_dims, sc->d_numeric_dims, ctx->d_sel, ctx->d_tie, sc->d_tie_score, slots, list, ctx->d_tie_count);
+            KB_LAUNCH_CHECK(ctx);
+            tpe_rescore_kernel<<<dim3(RS_GRID_X, (unsigned)ctx->n_numeric), RS_THREADS, 0, s>>>(ctx->d_dims, sc->d_numeric_dims, slots,
+                                                                                             list, ctx->d_tie_count);
+            KB_LAUNCH_CHECK(ctx);
+        }
+        tpe_pick_kernel<<<D, RS_THREADS, 0, s>>>(ctx->d_dims, ctx->d_sel, ctx->tie_slots, (const KbCand *)ctx->d_tie_list,
+                                                  ctx->d_tie_count, ctx->d_win, idx_base);
         KB_LAUNCH_CHECK(ctx);
     }
-    tpe_pick_kernel<<<(D + 127) / 128, 128, 0, s>>>(ctx->d_dims, D, ctx->d_sel, (const KbPartial *)sc->d_partial, ctx->d_win, idx_base);
-    delete pf3;
-    KB_LAUNCH_CHECK(ctx);
     int world = 1, rank = 0;
     kb_comm_world(ctx, &world, &rank);
     if (world > 1) {
@@ -660,7 +769,7 @@ static int tpe_finish_selection(kb_ctx *ctx, long long idx_base, int64_t *out_in
     for (int d = 0; d < D; d++) {
         if (hsel[(size_t)d].overflow)
             return kb_fail(ctx, KB_ERR_OVERFLOW, "kb_tpe_score_select: near-tie table of parameter %d overflowed (%u slots)", d,
-                           KB_TIE_SLOTS);
+                           ctx->tie_slots);
         if (out_index) out_index[d] = sc->h_win[d].index;
         if (out_value) out_value[d] = sc->h_win[d].value;
         if (out_score) out_score[d] = sc->h_win[d].score;
@@ -680,7 +789,7 @@ static int tpe_run_host(kb_ctx *ctx, int64_t n_cand, const double *cand, int64_t
     const int D = ctx->D;
     cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
     const int64_t rows = n_cand < KB_CHUNK_ROWS ? (n_cand > 0 ? n_cand : 1) : KB_CHUNK_ROWS;
-    int rc = tpe_ensure_scratch(ctx, rows, true, scores_host != nullptr);
+    int rc = tpe_ensure_scratch(ctx, rows, n_cand, true, scores_host != nullptr);
     if (rc) return rc;
     if (select && (rc = tpe_reset_selection(ctx, s))) return rc;
     const int64_t cap = ctx->chunk_cap;
@@ -737,7 +846,7 @@ extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const dou
     if (rc) return rc;
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
     const int64_t rows = n_cand < KB_CHUNK_ROWS ? (n_cand > 0 ? n_cand : 1) : KB_CHUNK_ROWS;
-    if ((rc = tpe_ensure_scratch(ctx, rows, false, false))) return rc;
+    if ((rc = tpe_ensure_scratch(ctx, rows, n_cand, false, false))) return rc;
     if ((rc = tpe_reset_selection(ctx, s))) return rc;
     const int64_t cap = ctx->chunk_cap;
     for (int64_t off = 0; off < n_cand; off += cap) {
