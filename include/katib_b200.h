@@ -113,6 +113,23 @@ int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const double *cand_d
                                int64_t index_offset, int64_t *out_index, double *out_value,
                                double *out_score, void *stream);
 
+/* No counterpart in the reference.  kb_tpe_scores for ONE continuous (UNIFORM) parameter, for callers that cannot
+ * allocate GPU memory when they need scores (a plugin inside an application that owns all device memory through its
+ * own pool, a process whose memory was handed out at start-up, a loop that must not hit cudaMalloc's device
+ * synchronisation).  It needs no kb_ctx and calls no cudaMalloc / cudaFree / allocating routine: the caller passes the
+ * candidates, both Parzen estimators (as kb_tpe_get_parzen returns them: w, mu, sigma, K entries per side) and the
+ * output as device pointers on `device`; scores[i] = log l(x_i) - log g(x_i).  Scratch is a static __device__ array
+ * inside the library (256 KiB + 256 B, resident on every GPU that loads the library until the process exits), which
+ * limits each side to 4096 components; larger K is refused with KB_ERR_UNSUPPORTED.  The first call on a device
+ * looks up the array's address (cudaGetSymbolAddress) -- make it before any stream capture starts.  All calls on a
+ * device share the array: it keeps the previous call's contents (every call rewrites what it reads, nothing has to be
+ * zero), and two calls that overlap on the GPU race, so serialise them.  Errors: kb_last_error(NULL). */
+int kb_tpe_scores_noalloc(int device, int64_t n_cand, const double *cand_device, int K_below,
+                          const double *w_below_device, const double *mu_below_device,
+                          const double *sigma_below_device, int K_above, const double *w_above_device,
+                          const double *mu_above_device, const double *sigma_above_device, double low,
+                          double high, double *scores_device, void *stream);
+
 /* Full tpe.Sampler.Sample for every parameter (sample.go:48-90): draw n_ei_candidates from l(x)
  * on the device (Philox4x32-10 keyed by seed; goptuna's math/rand stream is not reproducible),
  * score, select.  out_value[n_params] in internal representation. */

@@ -80,6 +80,7 @@ def lib():
         "kb_random_fill": ([vp, u64, u64, i64, vp], i32),
         "kb_peak_measure": ([vp, i32, C.POINTER(dbl)], i32),
         "kb_launch_count": ([vp], i64),
+        "kb_tpe_scores_noalloc": ([i32, i64, vp, i32, vp, vp, vp, i32, vp, vp, vp, dbl, dbl, vp, vp], i32),
         "kb_profile": ([vp, i32], i32),
         "kb_profile_read": ([vp, i32, C.POINTER(dbl), C.POINTER(i64)], i32),
     }
@@ -96,6 +97,14 @@ def _f64(a):
 
 def _ptr(a):
     return None if a is None else a.ctypes.data
+
+
+def tpe_scores_noalloc(device, n_cand, cand_ptr, below, above, low, high, out_ptr, stream=None):
+    """kb_tpe_scores_noalloc on raw device pointers; below/above = (K, w_ptr, mu_ptr, sigma_ptr)."""
+    rc = lib().kb_tpe_scores_noalloc(device, n_cand, cand_ptr, below[0], below[1], below[2], below[3], above[0], above[1],
+                                     above[2], above[3], low, high, out_ptr, stream)
+    if rc:
+        raise KbError(rc, lib().kb_last_error(None).decode())
 
 
 class Context:
