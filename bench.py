@@ -247,8 +247,9 @@ def main():
         ctx.comm_init(world, rank, uid[0])
     ctx.space_set(kinds, lows, highs, steps, nch)
     ctx.tpe_set_history(vals, loss)
-    n_local = n_total // world
-    offset = rank * n_local
+    from katib_b200.sharding import shard_range
+    offset, end = shard_range(n_total, world, rank)
+    n_local = end - offset
     cand = device_candidates(torch, kinds, lows, highs, steps, nch, n_local, 55 + rank, dev)
     torch.cuda.synchronize()
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)

@@ -1,0 +1,31 @@
+"""Host-side sharding rules of the multi-GPU TPE path (one process per GPU).
+
+The candidate set is split into contiguous index ranges; every rank scores its range and reports, per parameter, its
+local winner as (FP64 score, global index, value).  The global winner is the best score, lowest global index on ties --
+the rule tpe.Sampler.compare applies to the unsharded set (first maximum wins).  The CUDA side does the same merge in
+tpe_merge_kernel after one ncclAllGather; this module is the rule written once for bench.py and the CPU (gloo) tests.
+"""
+import numpy as np
+
+
+def shard_range(n_total, world, rank):
+    """[begin, end) of rank's contiguous slice; the first n_total % world ranks take one extra candidate."""
+    base, extra = divmod(n_total, world)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+def merge_winners(scores, indices, values):
+    """scores/indices/values: [world, D] arrays of local winners (index < 0 = rank had no candidate).
+    Returns ([D] score, [D] index, [D] value) of the global winners."""
+    scores, indices, values = np.asarray(scores, float), np.asarray(indices, np.int64), np.asarray(values, float)
+    world, D = scores.shape
+    out_s, out_i, out_v = np.full(D, -np.inf), np.full(D, -1, np.int64), np.zeros(D)
+    for d in range(D):
+        for r in range(world):
+            if indices[r, d] < 0:
+                continue
+            better = out_i[d] < 0 or scores[r, d] > out_s[d] or (scores[r, d] == out_s[d] and indices[r, d] < out_i[d])
+            if better:
+                out_s[d], out_i[d], out_v[d] = scores[r, d], indices[r, d], values[r, d]
+    return out_s, out_i, out_v
