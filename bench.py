@@ -192,6 +192,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0, help="candidates in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
+    os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "WARN")  # keep NCCL's banner off stdout (one JSON line)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -319,7 +320,18 @@ def main():
         else:
             e2e = {"value": None, "unit": "candidates/s", "note": pinned_note}
 
+    def shutdown():
+        # orderly exit on every rank: the library's NCCL communicator goes first, on all ranks together, then torch's
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ctx.close()
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+
     if rank != 0:
+        shutdown()
         return
     # ---- roofline from the live per-kernel event times (this rank's slice; every rank does the same work)
     n_cont, n_quant = 20, 10
@@ -364,9 +376,8 @@ def main():
                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
-    print(json.dumps(out))
-    if dist is not None:
-        dist.destroy_process_group()
+    print(json.dumps(out), flush=True)
+    shutdown()
 
 
 if __name__ == "__main__":
