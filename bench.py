@@ -192,7 +192,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0, help="candidates in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
-    os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "WARN")  # keep NCCL's banner off stdout (one JSON line)
+    os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "NONE")  # NCCL prints its version banner on stdout from level VERSION up; stdout carries one JSON line
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

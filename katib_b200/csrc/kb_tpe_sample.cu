@@ -1,0 +1,167 @@
+// kb_tpe_sample.cu -- candidate generation on the device: the first half of tpe.Sampler.Sample.
+//
+// Replaces (goptuna v0.8.0, not in the reference tree, go.mod:8; reached from sample.go:48-90):
+//   Sampler.sampleFromGMM              -> tpe_sample_kernel, numeric parameters: pick a component of the BELOW
+//                                         mixture by its weight, draw N(mu, sigma), reject until low <= x < high,
+//                                         then round to the quantum (Go math.Round: half away from zero)
+//   Sampler.sampleFromCategoricalDist  -> same kernel, categorical parameters: inverse CDF over p_below
+//   goptuna.RandomSampler.Sample       -> random_fill_kernel (converter.go:96-106, and TPE's start-up phase)
+// goptuna draws from Go's math/rand (not reproducible outside Go), so only the distribution can be matched; the
+// stream here is Philox4x32-10 keyed by the caller's seed with counter (candidate index, parameter, attempt).
+#include <math.h>
+
+#include "kb_internal.cuh"
+
+struct Philox {
+    uint32_t k0, k1;
+    __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
+    __device__ uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
+        uint32_t a = k0, b = k1;
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+            const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+            c0 = hi1 ^ c1 ^ a; c1 = lo1; c2 = hi0 ^ c3 ^ b; c3 = lo0;
+            a += 0x9E3779B9u; b += 0xBB67AE85u;
+        }
+        return make_uint4(c0, c1, c2, c3);
+    }
+};
+// 53-bit uniform in [0,1) from two 32-bit words
+__device__ __forceinline__ double u01(uint32_t a, uint32_t b) {
+    return (double)(((unsigned long long)a << 21) ^ (unsigned long long)(b >> 11)) * (1.0 / 9007199254740992.0);
+}
+
+#define SAMPLE_MAX_TRIES 4096
+
+// one thread per (candidate, parameter); lanes run along the parameter so row-major stores coalesce
+__global__ void tpe_sample_kernel(const KbDim *__restrict__ dims, int D, long long n, uint64_t seed, long long first,
+                                  double *__restrict__ out) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * D) return;
+    const long long i = t / D;
+    const int d = (int)(t % D);
+    const KbDim &dm = dims[d];
+    const Philox ph(seed);
+    const unsigned long long gi = (unsigned long long)(first + i);
+    double result;
+    if (dm.kind == KB_CATEGORICAL) {
+        const uint4 r = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d, 0u);
+        const double u = u01(r.x, r.y);
+        const double *p = dm.cat_p[0];
+        double acc = 0.0;
+        int c = dm.n_choices - 1;
+        for (int e = 0; e < dm.n_choices; e++) { acc += p[e]; if (u < acc) { c = e; break; } }
+        result = (double)c;
+    } else {
+        const int K = dm.K[0];
+        const double *w = dm.w[0], *mu = dm.mu[0], *sg = dm.sigma[0];
+        double x = 0.5 * (dm.lo + dm.hi);
+        for (uint32_t attempt = 0; attempt < SAMPLE_MAX_TRIES; attempt++) {
+            const uint4 r = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d, attempt + 1u);
+            const uint4 r2 = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d | 0x80000000u, attempt + 1u);
+            const double u = u01(r.x, r.y);
+            double acc = 0.0;
+            int a = K - 1;
+            for (int j = 0; j < K; j++) { acc += w[j]; if (u < acc) { a = j; break; } }
+            double u1 = u01(r.z, r.w), u2 = u01(r2.x, r2.y);
+            u1 = u1 < 1e-300 ? 1e-300 : u1;
+            const double z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);  // Box-Muller
+            const double draw = mu[a] + sg[a] * z;
+            if (dm.lo <= draw && draw < dm.hi) { x = draw; break; }
+        }
+        if (dm.q > 0.0) x = round(x / dm.q) * dm.q;
+        result = x;
+    }
+    out[i * D + d] = result;
+}
+
+// goptuna.RandomSampler: uniform over each distribution, internal representation
+__global__ void random_fill_kernel(const KbDim *__restrict__ dims, int D, long long n, uint64_t seed, unsigned long long first,
+                                   double *__restrict__ out) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * D) return;
+    const long long i = t / D;
+    const int d = (int)(t % D);
+    const KbDim &dm = dims[d];
+    const Philox ph(seed ^ 0x5bd1e995a5a5a5a5ull);
+    const unsigned long long gi = first + (unsigned long long)i;
+    const uint4 r = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d, 0u);
+    const double u = u01(r.x, r.y);
+    double v;
+    switch (dm.kind) {
+        case KB_UNIFORM: v = u * (dm.ext_hi - dm.ext_lo) + dm.ext_lo; break;
+        case KB_INT: v = floor(u * (dm.ext_hi - dm.ext_lo + 1.0)) + dm.ext_lo; v = fmin(v, dm.ext_hi); break;
+        case KB_STEP_INT: {
+            const double steps = floor((dm.ext_hi - dm.ext_lo) / dm.q);
+            v = fmin(floor(u * (steps + 1.0)), steps) * dm.q + dm.ext_lo;
+            break;
+        }
+        case KB_DISCRETE: {  // sample on the shifted grid [ -q/2, r + q/2 ), round, shift back, clamp
+            const double s = u * (dm.hi - dm.lo) + dm.lo;
+            v = round(s / dm.q) * dm.q + dm.shift;
+            v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
+            break;
+        }
+        default: v = fmin(floor(u * (double)dm.n_choices), (double)(dm.n_choices - 1)); break;
+    }
+    out[i * D + d] = v;
+}
+
+static int sample_launch(kb_ctx *ctx, int64_t n, uint64_t seed, double *d_out, cudaStream_t s) {
+    const long long total = (long long)n * ctx->D;
+    if (total == 0) return KB_OK;
+    KbProf pf(ctx, 6, s);
+    tpe_sample_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(ctx->d_dims, ctx->D, n, seed, 0, d_out);
+    KB_LAUNCH_CHECK(ctx);
+    return KB_OK;
+}
+
+extern "C" int kb_tpe_sample_candidates(kb_ctx *ctx, int64_t n, uint64_t seed, double *cand_host, double *cand_device,
+                                        void *stream) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_sample_candidates: call kb_tpe_set_history first");
+    if (n < 0 || n >= (1ll << 32)) return kb_fail(ctx, KB_ERR_UNSUPPORTED, "kb_tpe_sample_candidates: n outside [0, 2^32)");
+    if (n > 0 && !cand_host && !cand_device) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_sample_candidates: no output buffer");
+    if (n == 0) return KB_OK;
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    double *d_out = cand_device;
+    if (!d_out) KB_CUDA(ctx, cudaMalloc(&d_out, sizeof(double) * (size_t)n * ctx->D));
+    int rc = sample_launch(ctx, n, seed, d_out, s);
+    if (rc == KB_OK && cand_host) {
+        cudaError_t e = cudaMemcpyAsync(cand_host, d_out, sizeof(double) * (size_t)n * ctx->D, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) rc = kb_fail(ctx, KB_ERR_CUDA, "kb_tpe_sample_candidates: D2H: %s", cudaGetErrorString(e));
+    }
+    if (!cand_device) cudaFree(d_out);
+    return rc;
+}
+
+extern "C" int kb_random_fill(kb_ctx *ctx, uint64_t seed, uint64_t first_index, int64_t n, double *out) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (ctx->D == 0) return kb_fail(ctx, KB_ERR_STATE, "kb_random_fill: call kb_space_set first");
+    if (n < 0) return kb_fail(ctx, KB_ERR_INVALID, "kb_random_fill: n < 0");
+    if (n == 0) return KB_OK;
+    if (!out) return kb_fail(ctx, KB_ERR_INVALID, "kb_random_fill: out is NULL");
+    cudaStream_t s = ctx->stream;
+    double *d_out = nullptr;
+    KB_CUDA(ctx, cudaMalloc(&d_out, sizeof(double) * (size_t)n * ctx->D));
+    const long long total = (long long)n * ctx->D;
+    random_fill_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(ctx->d_dims, ctx->D, n, seed, first_index, d_out);
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, sizeof(double) * (size_t)total, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return kb_fail(ctx, KB_ERR_CUDA, "kb_random_fill: %s", cudaGetErrorString(e));
+    return KB_OK;
+}
+
+// device-side draw used by kb_tpe_suggest (kb_tpe_score.cu): same stream, no host copy
+int kb_tpe_sample_into(kb_ctx *ctx, int64_t n, uint64_t seed, double *d_out, cudaStream_t s) {
+    return sample_launch(ctx, n, seed, d_out, s);
+}

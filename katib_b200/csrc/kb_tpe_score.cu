@@ -855,3 +855,33 @@ extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const dou
     }
     return tpe_finish_selection(ctx, index_offset, out_index, out_value, out_score, s);
 }
+
+// Full tpe.Sampler.Sample for every parameter: draw on the device (kb_tpe_sample.cu), score, select.
+int kb_tpe_sample_into(kb_ctx *ctx, int64_t n, uint64_t seed, double *d_out, cudaStream_t s);
+
+extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t seed, double *out_value) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_suggest: call kb_tpe_set_history first");
+    if (n_ei_candidates < 1 || n_ei_candidates >= (1ll << 32))
+        return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest: n_ei_candidates outside [1, 2^32)");
+    if (!out_value) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest: out_value is NULL");
+    cudaStream_t s = ctx->stream;
+    const int64_t n = n_ei_candidates;
+    double *d_cand = nullptr;
+    KB_CUDA(ctx, cudaMalloc(&d_cand, sizeof(double) * (size_t)n * ctx->D));
+    int rc = kb_tpe_sample_into(ctx, n, seed, d_cand, s);
+    const int64_t rows = n < KB_CHUNK_ROWS ? n : KB_CHUNK_ROWS;
+    if (!rc) rc = tpe_ensure_scratch(ctx, rows, n, false, false);
+    if (!rc) rc = tpe_reset_selection(ctx, s);
+    const int64_t cap = ctx->chunk_cap;
+    for (int64_t off = 0; !rc && off < n; off += cap) {
+        const int m = (int)(n - off < cap ? n - off : cap);
+        rc = tpe_launch_chunk(ctx, d_cand + (size_t)off * ctx->D, m, off, off, true, nullptr, s);
+    }
+    if (!rc) rc = tpe_finish_selection(ctx, 0, nullptr, out_value, nullptr, s);
+    cudaStreamSynchronize(s);
+    cudaFree(d_cand);
+    return rc;
+}

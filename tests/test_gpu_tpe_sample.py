@@ -1,0 +1,100 @@
+"""On-device candidate generation (sampleFromGMM / sampleFromCategoricalDist / RandomSampler) and the full
+kb_tpe_suggest step.  goptuna's math/rand stream cannot be reproduced, so draws are compared in distribution with
+the oracle's sampler (two-sample Kolmogorov-Smirnov per parameter), and suggest is checked for self-consistency:
+it must equal score_select over the candidates the same seed generates."""
+import numpy as np
+import pytest
+from scipy import stats
+
+import _oracle as O
+import katib_b200 as kb
+from test_gpu_tpe import MIXED, make_history, working_domain
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = kb.Context(0)
+    yield c
+    c.close()
+
+
+def _setup(ctx, n_trials, seed):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    sp = MIXED
+    ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    vals = make_history(rng, n_trials, sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    loss = (vals[:, 0] - 1.0) ** 2 + 0.05 * (vals[:, 1] - 3) ** 2 + (vals[:, 2] != 1) + rng.normal(0, 0.5, n_trials)
+    ctx.tpe_set_history(vals, loss)
+    return sp, vals, loss
+
+
+def test_samples_follow_the_below_mixture(ctx):
+    sp, vals, loss = _setup(ctx, 400, 21)
+    n = 40000
+    cand = ctx.tpe_sample_candidates(n, seed=1234)
+    assert cand.shape == (n, len(sp["kinds"]))
+    for d, (k, lo, hi, st, c) in enumerate(zip(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])):
+        x = cand[:, d]
+        if k == kb.KB_CATEGORICAL:
+            pl, _ = O.categorical_tables(vals[:, d], loss, c)
+            freq = np.bincount(x.astype(int), minlength=c) / n
+            assert np.all(np.abs(freq - pl) < 5 * np.sqrt(pl * (1 - pl) / n) + 1e-3), (d, freq, pl)
+            continue
+        wl, wh, q, sh = working_domain(k, lo, hi, st)
+        below, _ = O.tpe_split(vals[:, d] - sh, loss)
+        w, mu, sg = O.parzen_build(below, wl, wh)
+        ref = np.zeros(n)
+        O.lib().kbo_gmm_sample(99, n, len(w), w, mu, sg, wl, wh, q, ref)
+        if q > 0:
+            assert np.allclose(x / q, np.round(x / q)) and x.min() >= wl and x.max() <= wh
+            lv = np.unique(np.concatenate([x, ref]))
+            fa = np.array([(x == v).mean() for v in lv]); fb = np.array([(ref == v).mean() for v in lv])
+            assert np.max(np.abs(np.cumsum(fa) - np.cumsum(fb))) < 0.02, d
+        else:
+            assert x.min() >= wl and x.max() < wh
+            ks = stats.ks_2samp(x, ref).statistic
+            assert ks < 0.02, (d, ks)
+
+
+def test_samples_are_deterministic_and_seeded(ctx):
+    _setup(ctx, 120, 22)
+    a = ctx.tpe_sample_candidates(500, seed=7)
+    b = ctx.tpe_sample_candidates(500, seed=7)
+    c = ctx.tpe_sample_candidates(500, seed=8)
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    assert np.array_equal(ctx.tpe_sample_candidates(200, seed=7), a[:200])  # counter-based: prefix-stable
+
+
+@pytest.mark.parametrize("n_ei", [1, 24, 1000])
+def test_suggest_equals_select_over_its_own_candidates(ctx, n_ei):
+    sp, vals, loss = _setup(ctx, 300, 23)
+    out = ctx.tpe_suggest(n_ei, seed=42)
+    cand = ctx.tpe_sample_candidates(n_ei, seed=42)
+    idx, val, sc = ctx.tpe_score_select(cand)
+    assert np.array_equal(out, val)
+    for d, k in enumerate(sp["kinds"]):  # the suggestion lies inside the distribution
+        if k == kb.KB_CATEGORICAL:
+            assert 0 <= out[d] < sp["nch"][d]
+        else:
+            assert sp["lows"][d] <= out[d] <= sp["highs"][d]
+
+
+def test_random_fill_ranges_and_uniformity(ctx):
+    sp = MIXED
+    ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    n = 30000
+    r = ctx.random_fill(seed=5, first=0, n=n)
+    assert np.array_equal(ctx.random_fill(seed=5, first=100, n=50), r[100:150])
+    for d, (k, lo, hi, st, c) in enumerate(zip(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])):
+        x = r[:, d]
+        if k == kb.KB_UNIFORM:
+            assert x.min() >= lo and x.max() < hi and stats.kstest((x - lo) / (hi - lo), "uniform").statistic < 0.02
+        elif k == kb.KB_CATEGORICAL:
+            assert set(np.unique(x)) == set(range(c))
+        elif k == kb.KB_INT:
+            assert x.min() == lo and x.max() == hi and np.all(x == np.round(x))
+        else:
+            g = (x - lo) / st
+            assert np.allclose(g, np.round(g)) and x.min() >= lo and x.max() <= hi
