@@ -1,0 +1,307 @@
+// kb_linalg.cu -- the two dense FP64 building blocks of the CMA-ES path.
+//
+//  kb_dgemm_nt   C[M x N] = alpha * (A[M x K] * diag(s)) * Bm[N x K]^T + beta * C      (row-major, K contiguous in
+//                both operands).  FP64 tensor cores: mma.sync.m8n8k4.f64 (DMMA) -- tcgen05 has no FP64 kind, so on
+//                sm_100a this is the tensor path for the precision north_star demands (1e-9 parity).  Every dense
+//                contraction of ask/tell is this one form (see kb_cmaes.cu).
+//  kb_eigh_device  symmetric eigendecomposition by one-sided (Hestenes) parallel Jacobi, standing in for gonum's
+//                mat.EigenSym behind goptuna's cmaes.Optimizer.eigenDecomposition (module not in the reference tree,
+//                go.mod:141; reached from sample.go:39).  Columns of G = A are orthogonalised by plane rotations in
+//                round-robin (chess-tournament) order, n/2 disjoint pairs per step, one warp per pair; V accumulates
+//                the rotations.  At convergence G = V Lambda.  One CTA (block barrier) for small n, a cooperative
+//                grid (grid.sync) above.
+#include <cooperative_groups.h>
+#include <math.h>
+
+#include "kb_internal.cuh"
+#include "kb_linalg.cuh"
+
+namespace cg = cooperative_groups;
+
+// ---------------------------------------------------------------------------------------------------------------
+// DMMA GEMM, NT form.  CTA tile 64 x 64, 4 warps (2 x 2), warp tile 32 x 32 = 4 x 4 m8n8k4 tiles, BK = 16.
+// ---------------------------------------------------------------------------------------------------------------
+#define GM_BM 64
+#define GM_BN 64
+#define GM_BK 16
+#define GM_LD (GM_BK + 1)  // padded leading dimension (doubles): rows 17 apart -> fragment loads hit distinct banks
+
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(128)
+dgemm_nt_kernel(int M, int N, int K, const double *__restrict__ A, int lda, const double *__restrict__ s,
+                const double *__restrict__ Bm, int ldb, double *__restrict__ C, int ldc, double alpha, double beta) {
+    __shared__ double As[2][GM_BM][GM_LD];
+    __shared__ double Bs[2][GM_BN][GM_LD];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.y * GM_BM, n0 = blockIdx.x * GM_BN;
+    const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    // each thread moves 8 doubles of A and 8 of Bm per stage: row = tid / 2, 8 consecutive k
+    const int lr = tid >> 1, lk = (tid & 1) * 8;
+    auto load_stage = [&](int buf, int k0) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const int k = k0 + lk + e;
+            double a = 0.0, b = 0.0;
+            if (k < K) {
+                if (m0 + lr < M) { a = A[(size_t)(m0 + lr) * lda + k]; if (s) a *= s[k]; }
+                if (n0 + lr < N) b = Bm[(size_t)(n0 + lr) * ldb + k];
+            }
+            As[buf][lr][lk + e] = a;
+            Bs[buf][lr][lk + e] = b;
+        }
+    };
+    const int nk = (K + GM_BK - 1) / GM_BK;
+    load_stage(0, 0);
+    __syncthreads();
+    for (int kt = 0; kt < nk; kt++) {
+        const int buf = kt & 1;
+        if (kt + 1 < nk) load_stage(buf ^ 1, (kt + 1) * GM_BK);
+#pragma unroll
+        for (int kk = 0; kk < GM_BK; kk += 4) {
+            double af[4], bf[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) af[i] = As[buf][wm + i * 8 + g][kk + t];
+#pragma unroll
+            for (int j = 0; j < 4; j++) bf[j] = Bs[buf][wn + j * 8 + g][kk + t];
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) dmma_m8n8k4(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+        }
+        __syncthreads();
+    }
+    // C fragment: row = g, cols = 2t, 2t+1
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int r = m0 + wm + i * 8 + g, c = n0 + wn + j * 8 + 2 * t;
+            if (r < M) {
+#pragma unroll
+                for (int e = 0; e < 2; e++)
+                    if (c + e < N) {
+                        double *p = C + (size_t)r * ldc + c + e;
+                        *p = beta == 0.0 ? alpha * acc[i][j][e] : alpha * acc[i][j][e] + beta * *p;
+                    }
+            }
+        }
+}
+
+int kb_dgemm_nt(kb_ctx *ctx, int M, int N, int K, const double *A, int lda, const double *s, const double *Bm, int ldb,
+                double *C, int ldc, double alpha, double beta, cudaStream_t st) {
+    if (M <= 0 || N <= 0) return KB_OK;
+    dim3 grid((unsigned)((N + GM_BN - 1) / GM_BN), (unsigned)((M + GM_BM - 1) / GM_BM));
+    dgemm_nt_kernel<<<grid, 128, 0, st>>>(M, N, K, A, lda, s, Bm, ldb, C, ldc, alpha, beta);
+    KB_LAUNCH_CHECK(ctx);
+    return KB_OK;
+}
+
+__global__ void transpose_kernel(int rows, int cols, const double *__restrict__ in, double *__restrict__ out) {
+    __shared__ double tile[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int r = r0 + j, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[j][threadIdx.x] = in[(size_t)r * cols + c];
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int c = c0 + j, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) out[(size_t)c * rows + r] = tile[threadIdx.x][j];
+    }
+}
+
+int kb_transpose(kb_ctx *ctx, int rows, int cols, const double *in, double *out, cudaStream_t st) {
+    dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
+    transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(rows, cols, in, out);
+    KB_LAUNCH_CHECK(ctx);
+    return KB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// one-sided Jacobi.  Storage: Gt[j*n + i] = G[i][j] (column j contiguous), same for Vt.
+// ---------------------------------------------------------------------------------------------------------------
+#define EG_THREADS 256
+#define EG_MAX_SWEEPS 40
+
+struct EighShared {   // device scalars
+    int rotated;      // rotations applied in the current sweep
+    int sweeps;
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// round-robin pairing of N (even) players, round r in [0, N-1): pair index i in [0, N/2)
+__device__ __forceinline__ void rr_pair(int N, int r, int i, int &p, int &q) {
+    if (i == 0) { p = N - 1; q = r; }
+    else { p = (r + i) % (N - 1); q = (r - i + (N - 1)) % (N - 1); }
+    if (p > q) { int t = p; p = q; q = t; }
+}
+
+template <bool GRID>
+__global__ void __launch_bounds__(EG_THREADS)
+jacobi_onesided_kernel(int n, double *Gt, double *Vt, EighShared *sh, double tol) {
+    const int warps_per_block = EG_THREADS / 32;
+    const int gw = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+    const int total_warps = gridDim.x * warps_per_block;
+    const int lane = threadIdx.x & 31;
+    const int N = n + (n & 1);  // pad to even; player n (if any) is a bye
+    cg::grid_group grid = cg::this_grid();
+    for (int sweep = 0; sweep < EG_MAX_SWEEPS; sweep++) {
+        for (int r = 0; r < N - 1; r++) {
+            for (int i = gw; i < N / 2; i += total_warps) {
+                int p, q;
+                rr_pair(N, r, i, p, q);
+                if (q >= n) continue;
+                double *gp = Gt + (size_t)p * n, *gq = Gt + (size_t)q * n;
+                double a = 0.0, b = 0.0, c = 0.0;
+                for (int k = lane; k < n; k += 32) {
+                    const double x = gp[k], y = gq[k];
+                    a += x * x; b += y * y; c += x * y;
+                }
+                a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+                if (fabs(c) <= tol * sqrt(a * b) || c == 0.0) continue;
+                const double zeta = (b - a) / (2.0 * c);
+                const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+                double *vp = Vt + (size_t)p * n, *vq = Vt + (size_t)q * n;
+                for (int k = lane; k < n; k += 32) {
+                    const double x = gp[k], y = gq[k];
+                    gp[k] = cs * x - sn * y; gq[k] = sn * x + cs * y;
+                    const double u = vp[k], v = vq[k];
+                    vp[k] = cs * u - sn * v; vq[k] = sn * u + cs * v;
+                }
+                if (lane == 0) atomicAdd(&sh->rotated, 1);
+            }
+            if (GRID) grid.sync(); else __syncthreads();
+        }
+        const int rot = *(volatile int *)&sh->rotated;
+        if (GRID) grid.sync(); else __syncthreads();
+        if (blockIdx.x == 0 && threadIdx.x == 0) { sh->rotated = 0; sh->sweeps = sweep + 1; }
+        if (GRID) grid.sync(); else __syncthreads();
+        if (rot == 0) break;
+    }
+}
+
+// lambda_j = v_j . g_j (keeps the sign for indefinite input), then rank by value, canonical signs, write outputs:
+//   w[rank] = lambda, V[i*n + rank] = +-v_j[i]  (row-major, eigenvector `rank` in column `rank`)
+__global__ void eigh_finish_kernel(int n, const double *__restrict__ Gt, const double *__restrict__ Vt, double shift,
+                                   double *lam, double *w, double *V) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp < n) {
+        double acc = 0.0;
+        for (int k = lane; k < n; k += 32) acc += Vt[(size_t)warp * n + k] * Gt[(size_t)warp * n + k];
+        acc = warp_sum(acc);
+        if (lane == 0) lam[warp] = acc - shift;
+    }
+}
+__global__ void eigh_order_kernel(int n, const double *__restrict__ Vt, const double *__restrict__ lam, double *w, double *V) {
+    const int j = blockIdx.x;  // source column
+    __shared__ int s_rank;
+    __shared__ double s_sign;
+    if (threadIdx.x == 0) {
+        const double lj = lam[j];
+        int r = 0;
+        for (int e = 0; e < n; e++) { const double le = lam[e]; r += (le < lj || (le == lj && e < j)) ? 1 : 0; }
+        s_rank = r;
+        double big = 0.0, sv = 1.0;
+        for (int k = 0; k < n; k++) { const double v = Vt[(size_t)j * n + k]; if (fabs(v) > big) { big = fabs(v); sv = v < 0 ? -1.0 : 1.0; } }
+        s_sign = sv;
+        w[r] = lj;
+    }
+    __syncthreads();
+    const int r = s_rank;
+    const double sg = s_sign;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) V[(size_t)k * n + r] = sg * Vt[(size_t)j * n + k];
+}
+
+__global__ void eigh_init_kernel(int n, const double *__restrict__ A, double shift, double *Gt, double *Vt, EighShared *sh) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx == 0) { sh->rotated = 0; sh->sweeps = 0; }
+    if (idx >= (size_t)n * n) return;
+    const int j = (int)(idx / n), i = (int)(idx % n);
+    // symmetrise as the reference does before factorising: (C + C^T) / 2
+    Gt[idx] = 0.5 * (A[(size_t)i * n + j] + A[(size_t)j * n + i]) + (i == j ? shift : 0.0);
+    Vt[idx] = i == j ? 1.0 : 0.0;
+}
+
+// workspace: Gt, Vt (n*n each), lam (n), EighShared
+size_t kb_eigh_workspace_bytes(int n) { return sizeof(double) * ((size_t)2 * n * n + n) + 256; }
+
+int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *d_w, double *d_V, void *workspace,
+                   cudaStream_t st) {
+    double *Gt = (double *)workspace, *Vt = Gt + (size_t)n * n, *lam = Vt + (size_t)n * n;
+    EighShared *sh = (EighShared *)(lam + n + (n & 1));
+    KbProf pf(ctx, 9, st);
+    eigh_init_kernel<<<(unsigned)(((size_t)n * n + 255) / 256), 256, 0, st>>>(n, d_A, shift, Gt, Vt, sh);
+    KB_LAUNCH_CHECK(ctx);
+    const double tol = sqrt((double)n) * 2.220446049250313e-16;  // LAPACK dgesvj-style stopping criterion
+    const int pairs = (n + 1) / 2;
+    const int warps_per_block = EG_THREADS / 32;
+    if (pairs <= warps_per_block * 2) {
+        jacobi_onesided_kernel<false><<<1, EG_THREADS, 0, st>>>(n, Gt, Vt, sh, tol);
+        KB_LAUNCH_CHECK(ctx);
+    } else {
+        int blocks = (pairs + warps_per_block - 1) / warps_per_block;
+        int per_sm = 0;
+        KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_onesided_kernel<true>, EG_THREADS, 0));
+        const int cap = per_sm * ctx->prop.multiProcessorCount;
+        if (blocks > cap) blocks = cap;
+        double tolv = tol;
+        void *args[] = {&n, &Gt, &Vt, &sh, &tolv};
+        KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_onesided_kernel<true>, dim3((unsigned)blocks), dim3(EG_THREADS), args, 0, st));
+        ctx->launches++;
+    }
+    eigh_finish_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(n, Gt, Vt, shift, lam, d_w, d_V);
+    KB_LAUNCH_CHECK(ctx);
+    eigh_order_kernel<<<(unsigned)n, 128, 0, st>>>(n, Vt, lam, d_w, d_V);
+    KB_LAUNCH_CHECK(ctx);
+    return KB_OK;
+}
+
+extern "C" int kb_eigh(kb_ctx *ctx, int n, const double *A, double *w, double *V) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (n < 1 || n > 4096) return kb_fail(ctx, KB_ERR_UNSUPPORTED, "kb_eigh: n=%d outside [1,4096]", n);
+    if (!A || !w || !V) return kb_fail(ctx, KB_ERR_INVALID, "kb_eigh: NULL buffer");
+    // one-sided Jacobi resolves eigenvectors of A^2: shift an indefinite matrix positive (Gershgorin bound) first
+    double shift = 0.0, low = INFINITY;
+    for (int i = 0; i < n; i++) {
+        double r = 0.0;
+        for (int j = 0; j < n; j++) if (j != i) r += fabs(0.5 * (A[(size_t)i * n + j] + A[(size_t)j * n + i]));
+        low = fmin(low, A[(size_t)i * n + i] - r);
+    }
+    bool spd_hint = true;  // diagonally "positive enough": keep the relative accuracy of small eigenvalues
+    for (int i = 0; i < n; i++) if (!(A[(size_t)i * n + i] > 0.0)) spd_hint = false;
+    if (!spd_hint && low < 0.0) shift = -low * 1.0625 + 1e-300;
+    cudaStream_t s = ctx->stream;
+    double *d = nullptr;
+    const size_t nn = (size_t)n * n;
+    KB_CUDA(ctx, cudaMalloc(&d, sizeof(double) * (2 * nn + n) + kb_eigh_workspace_bytes(n)));
+    double *d_A = d, *d_V = d + nn, *d_w = d_V + nn;
+    void *ws = (void *)(d_w + n + (n & 1));
+    cudaError_t e = cudaMemcpyAsync(d_A, A, sizeof(double) * nn, cudaMemcpyHostToDevice, s);
+    int rc = e == cudaSuccess ? kb_eigh_device(ctx, n, d_A, shift, d_w, d_V, ws, s) : kb_fail(ctx, KB_ERR_CUDA, "kb_eigh: H2D");
+    if (!rc) {
+        e = cudaMemcpyAsync(w, d_w, sizeof(double) * n, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(V, d_V, sizeof(double) * nn, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) rc = kb_fail(ctx, KB_ERR_CUDA, "kb_eigh: %s", cudaGetErrorString(e));
+    }
+    cudaFree(d);
+    return rc;
+}

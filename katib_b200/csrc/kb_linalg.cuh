@@ -1,0 +1,13 @@
+// kb_linalg.cuh -- dense FP64 helpers shared by kb_linalg.cu and kb_cmaes.cu (not part of the ABI).
+#pragma once
+#include "kb_internal.cuh"
+
+// C[M x N] = alpha * (A[M x K] * diag(s)) * Bm[N x K]^T + beta * C; row-major; s may be NULL; DMMA (mma.sync f64)
+int kb_dgemm_nt(kb_ctx *ctx, int M, int N, int K, const double *A, int lda, const double *s, const double *Bm, int ldb,
+                double *C, int ldc, double alpha, double beta, cudaStream_t st);
+int kb_transpose(kb_ctx *ctx, int rows, int cols, const double *in, double *out, cudaStream_t st);
+// symmetric eigendecomposition of (A + A^T)/2 + shift*I; w ascending (shift removed), V[i*n+j] = component i of
+// eigenvector j, canonical signs; workspace of kb_eigh_workspace_bytes(n) bytes
+size_t kb_eigh_workspace_bytes(int n);
+int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *d_w, double *d_V, void *workspace,
+                   cudaStream_t st);

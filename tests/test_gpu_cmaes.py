@@ -1,0 +1,171 @@
+"""CMA-ES parity on the GPU through the C ABI (FP64, tolerance 1e-9 relative as north_star states).
+
+What can be compared: the covariance update (m, sigma, C, p_sigma, p_c) is invariant to the eigensolver, so it is
+checked against the oracle and the numpy golden states directly.  Samples x = m + sigma B D z are NOT invariant to
+the sign/order of eigenvectors nor to the basis inside a degenerate eigenspace (SURVEY hard part 6), so ask() is
+checked (a) with the oracle's (B, D) fed through kb_cmaes_set_eig and (b) against the GPU's own canonical factors."""
+import os
+
+import numpy as np
+import pytest
+
+import _oracle as O
+import katib_b200 as kb
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = kb.Context(0)
+    yield c
+    c.close()
+
+
+def state_vec(st):
+    return np.concatenate([st["mean"], [st["sigma"]], st["C"].ravel(), st["p_sigma"], st["p_c"]])
+
+
+def close(a, b, rtol=RTOL):
+    scale = max(1.0, float(np.max(np.abs(b))))
+    return float(np.max(np.abs(a - b))) <= rtol * scale
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 17, 64, 200, 512])
+def test_eigh_vs_lapack(ctx, n):
+    rng = np.random.Generator(np.random.PCG64(n))
+    M = rng.normal(size=(n, n))
+    A = M @ M.T / n + np.diag(np.logspace(-3, 2, n))
+    w, V = ctx.eigh(A)
+    wr = np.linalg.eigvalsh(A)
+    np.testing.assert_allclose(w, wr, rtol=1e-11, atol=1e-13 * wr.max())
+    assert np.max(np.abs(V @ np.diag(w) @ V.T - A)) <= 1e-11 * np.abs(A).max()
+    assert np.max(np.abs(V.T @ V - np.eye(n))) <= 1e-11
+    assert np.all(np.diff(w) >= 0)
+    assert np.all(V[np.abs(V).argmax(axis=0), np.arange(n)] > 0)  # canonical sign
+
+
+def test_eigh_identity_and_indefinite(ctx):
+    w, V = ctx.eigh(np.eye(6))
+    assert np.array_equal(w, np.ones(6)) and np.array_equal(V, np.eye(6))
+    rng = np.random.Generator(np.random.PCG64(9))
+    M = rng.normal(size=(12, 12))
+    A = (M + M.T) / 2  # indefinite: handled by a Gershgorin shift
+    w, V = ctx.eigh(A)
+    np.testing.assert_allclose(w, np.linalg.eigvalsh(A), rtol=0, atol=1e-11 * np.abs(A).max() * 12)
+    assert np.max(np.abs(V @ np.diag(w) @ V.T - A)) <= 1e-10 * np.abs(A).max() * 12
+
+
+@pytest.mark.parametrize("n,lam", [(4, 8), (10, 0), (24, 48)])
+def test_tell_matches_golden_and_oracle(ctx, golden_dir, n, lam):
+    t = np.load(os.path.join(golden_dir, "cmaes_golden.npz"))
+    ctx.cmaes_create(np.full(n, 0.5), 1.3, lam)
+    opt = O.Cma(np.full(n, 0.5), 1.3, lam)
+    for gen in range(3):
+        xs, fs = t[f"n{n}_xs"][gen], t[f"n{n}_fs"][gen]
+        ctx.cmaes_tell(xs, fs)
+        opt.tell(xs, fs)
+        st = ctx.cmaes_state()
+        assert st["generation"] == gen + 1
+        assert close(state_vec(st), t[f"n{n}_states"][gen]), gen
+        assert close(state_vec(st), opt.state_vec()), gen
+
+
+def test_ask_with_oracle_factors_and_with_own(ctx):
+    rng = np.random.Generator(np.random.PCG64(77))
+    n, lam = 16, 32
+    mean = rng.normal(size=n)
+    ctx.cmaes_create(mean, 0.7, lam)
+    opt = O.Cma(mean, 0.7, lam)
+    xs = mean + 0.7 * rng.normal(size=(lam, n)) * np.linspace(0.3, 3, n)
+    fs = np.sum(xs ** 2 * np.arange(1, n + 1), axis=1)
+    ctx.cmaes_tell(xs, fs)
+    opt.tell(xs, fs)
+    z = rng.normal(size=(lam, n))
+    # (a) oracle's factors fed in: samples must agree to rounding
+    B, D = opt.eig()
+    ctx.cmaes_set_eig(B, D)
+    x_gpu = ctx.cmaes_ask(lam, z)
+    x_ref = opt.ask_batch(z)
+    assert close(x_gpu, x_ref, 1e-12)
+    # (b) the GPU's own canonical factors: x = m + sigma B D z, and B D^2 B^T = C
+    ctx.cmaes_tell(x_gpu, np.sum(x_gpu ** 2, axis=1))
+    st = ctx.cmaes_state(want_eig=True)
+    x2 = ctx.cmaes_ask(lam, z)
+    ref2 = st["mean"] + st["sigma"] * (z * st["D"]) @ st["B"].T
+    assert close(x2, ref2, 1e-12)
+    assert close(st["B"] @ np.diag(st["D"] ** 2) @ st["B"].T, st["C"])
+    assert np.max(np.abs(st["B"].T @ st["B"] - np.eye(n))) < 1e-12
+
+
+def test_generation0_is_identity(ctx):
+    ctx.cmaes_create(np.arange(5.0), 2.0, 6)
+    z = np.arange(30.0).reshape(6, 5) / 7
+    assert close(ctx.cmaes_ask(6, z), np.arange(5.0) + 2.0 * z, 1e-15)
+    st = ctx.cmaes_state(want_eig=True)
+    assert np.array_equal(st["B"], np.eye(5)) and np.array_equal(st["D"], np.ones(5))
+
+
+def test_closed_loop_20_generations(ctx):
+    """GPU asks (its own factors), the harness evaluates, both optimisers are told the same population."""
+    rng = np.random.Generator(np.random.PCG64(5))
+    n, lam = 32, 64
+    Q, _ = np.linalg.qr(rng.normal(size=(n, n)))
+    scale = np.logspace(0, 3, n)
+    fobj = lambda X: np.sum(((X - 1.0) @ Q) ** 2 * scale, axis=1)
+    m0 = np.full(n, 3.0)
+    ctx.cmaes_create(m0, 2.0, lam)
+    opt = O.Cma(m0, 2.0, lam)
+    f_first = None
+    for gen in range(20):
+        z = rng.normal(size=(lam, n))
+        X = ctx.cmaes_ask(lam, z)
+        f = fobj(X)
+        f_first = f_first if f_first is not None else f.mean()
+        ctx.cmaes_tell(X, f)
+        opt.tell(X, f)
+        assert close(state_vec(ctx.cmaes_state()), opt.state_vec()), gen
+    assert fobj(ctx.cmaes_state()["mean"][None])[0] < 0.05 * f_first  # it optimises
+
+
+def test_device_rng_ask_respects_bounds(ctx):
+    n, lam = 6, 4000
+    lo, hi = np.full(n, -1.0), np.full(n, 1.5)
+    ctx.cmaes_create(np.zeros(n), 1.0, 16, lo, hi)
+    X = ctx.cmaes_ask(lam, None, seed=3)
+    assert X.shape == (lam, n) and X.min() >= -1.0 and X.max() <= 1.5
+    assert np.array_equal(X, ctx.cmaes_ask(lam, None, seed=3))
+    assert not np.array_equal(X, ctx.cmaes_ask(lam, None, seed=4))
+    # resampling (not clipping) keeps the mass strictly inside: almost no point sits exactly on a bound
+    assert np.mean((X == -1.0) | (X == 1.5)) < 1e-3
+    ctx.cmaes_create(np.zeros(n), 1.0, 16)
+    Xu = ctx.cmaes_ask(20000, None, seed=1)
+    assert abs(Xu.mean()) < 0.02 and abs(Xu.std() - 1.0) < 0.02
+
+
+def test_config4_shape_one_generation(ctx):
+    """BASELINE configs[3] shape: n = 512, popsize 4096 (one generation; the CPU oracle needs ~10 s for it)."""
+    rng = np.random.Generator(np.random.PCG64(4))
+    n, lam = 512, 4096
+    m0 = np.full(n, 3.0)
+    ctx.cmaes_create(m0, 2.0, lam, np.full(n, -5.0), np.full(n, 5.0))
+    opt = O.Cma(m0, 2.0, lam)
+    z = rng.normal(size=(lam, n))
+    X = ctx.cmaes_ask(lam, z)
+    assert close(X, np.clip(m0 + 2.0 * z, -5.0, 5.0), 1e-14)
+    f = np.sum((X * np.logspace(0, 3, n)) ** 2, axis=1)
+    ctx.cmaes_tell(X, f)
+    opt.tell(X, f)
+    assert close(state_vec(ctx.cmaes_state()), opt.state_vec())
+    st = ctx.cmaes_state(want_eig=True)
+    assert close(st["B"] @ np.diag(st["D"] ** 2) @ st["B"].T, st["C"])
+
+
+def test_errors(ctx):
+    c2 = kb.Context(0)
+    with pytest.raises(kb.KbError):
+        c2.cmaes_ask(4, np.zeros((4, 3)))
+    with pytest.raises(kb.KbError):
+        c2.cmaes_create(np.zeros(3), -1.0)
+    c2.close()
