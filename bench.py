@@ -191,7 +191,14 @@ def main():
     ap.add_argument("--cand", type=int, default=26, help="log2 of the candidate count (26 = 64 Mi, the headline)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="candidates in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="tpe50", help="tpe50 (headline, configs[4]) | sobol | tpe20 | cmaes | tpe3")
     args = ap.parse_args()
+    if args.workload != "tpe50":
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_workloads
+        if int(os.environ.get("RANK", "0")) == 0:
+            bench_workloads.WORKLOADS[args.workload](args)
+        return
     os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "NONE")  # NCCL prints its version banner on stdout from level VERSION up; stdout carries one JSON line
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

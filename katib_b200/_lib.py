@@ -116,6 +116,7 @@ class Context:
         if rc:
             raise KbError(rc, lib().kb_last_error(None).decode())
         self.D = 0
+        self._cma_n = 0
 
     def close(self):
         if getattr(self, "_h", None):
