@@ -21,6 +21,7 @@
  */
 #ifndef KATIB_B200_H
 #define KATIB_B200_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -171,10 +172,34 @@ int kb_cmaes_set_eig(kb_ctx *ctx, const double *B, const double *D);
  * A[n x n] row-major -> w ascending, V[i*n+j] = component i of eigenvector j. */
 int kb_eigh(kb_ctx *ctx, int n, const double *A, double *w, double *V);
 
+/* Jacobi sweeps used by the most recent factorisation on this ctx (kb_eigh or the one inside ask/tell). */
+int kb_eigh_stats(const kb_ctx *ctx, int *sweeps);
+
 /* ---- random -----------------------------------------------------------------------------------
  * goptuna.RandomSampler (converter.go:96-106): out[i*n_params + d] uniform over each parameter's
  * distribution, internal representation, Philox keyed by (seed, first_index + i). */
 int kb_random_fill(kb_ctx *ctx, uint64_t seed, uint64_t first_index, int64_t n, double *out);
+
+/* ---- the suggestion service above the kernels ------------------------------------------------
+ * Host-side mirror of the reference's Go service (pkg/suggestion/v1beta1/goptuna/service.go:47-215 with
+ * converter.go and sample.go): search-space and settings parsing, trial conversion and state mapping, trial-name
+ * matching, the sampling loop and value formatting.  Requests and replies are serialized protobuf messages of
+ * pkg/apis/manager/v1beta1/api.proto (GetSuggestionsRequest -> GetSuggestionsReply,
+ * ValidateAlgorithmSettingsRequest -> empty reply), i.e. exactly the bytes the katib-controller puts on the wire, so
+ * a gRPC front end only forwards them.  Both calls return the gRPC status code the reference returns at the same spot
+ * (0 OK, 3 InvalidArgument, 13 Internal); kb_service_last_message gives the status text.  One kb_service per
+ * experiment, like one reference service process per Suggestion CR (composer.go:72-146). */
+typedef struct kb_service kb_service;
+int kb_service_create(int device, kb_service **out);
+int kb_service_destroy(kb_service *svc);
+/* SuggestionService.GetSuggestions (service.go:54-93).  *reply points into memory owned by svc, valid until the
+ * next call on it. */
+int kb_service_get_suggestions(kb_service *svc, const void *request, size_t request_len, const void **reply,
+                               size_t *reply_len);
+/* SuggestionService.ValidateAlgorithmSettings (service.go:173-211); request == NULL is the nil request.
+ * Needs no GPU. */
+int kb_service_validate_algorithm_settings(kb_service *svc, const void *request, size_t request_len);
+const char *kb_service_last_message(const kb_service *svc);
 
 /* ---- measurement helpers (used by bench.py and the profiles) ----------------------------------
  * which: 0 = MUFU.EX2 Gop/s, 1 = FP32 FFMA GFMA/s, 2 = FP64 DFMA GFMA/s, 3 = HBM write GB/s,

@@ -78,9 +78,15 @@ def lib():
         "kb_cmaes_set_eig": ([vp, vp, vp], i32),
         "kb_eigh": ([vp, i32, vp, vp, vp], i32),
         "kb_random_fill": ([vp, u64, u64, i64, vp], i32),
+        "kb_eigh_stats": ([vp, C.POINTER(i32)], i32),
         "kb_peak_measure": ([vp, i32, C.POINTER(dbl)], i32),
         "kb_launch_count": ([vp], i64),
         "kb_tpe_scores_noalloc": ([i32, i64, vp, i32, vp, vp, vp, i32, vp, vp, vp, dbl, dbl, vp, vp], i32),
+        "kb_service_create": ([i32, C.POINTER(vp)], i32),
+        "kb_service_destroy": ([vp], i32),
+        "kb_service_get_suggestions": ([vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)], i32),
+        "kb_service_validate_algorithm_settings": ([vp, vp, C.c_size_t], i32),
+        "kb_service_last_message": ([vp], C.c_char_p),
         "kb_profile": ([vp, i32], i32),
         "kb_profile_read": ([vp, i32, C.POINTER(dbl), C.POINTER(i64)], i32),
     }
@@ -105,6 +111,43 @@ def tpe_scores_noalloc(device, n_cand, cand_ptr, below, above, low, high, out_pt
                                      above[2], above[3], low, high, out_ptr, stream)
     if rc:
         raise KbError(rc, lib().kb_last_error(None).decode())
+
+
+class Service:
+    """kb_service: the suggestion service above the kernels.  Requests / replies are serialized protobuf bytes."""
+    OK, INVALID_ARGUMENT, INTERNAL = 0, 3, 13
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        rc = lib().kb_service_create(device, C.byref(self._h))
+        if rc:
+            raise KbError(rc, "kb_service_create failed")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().kb_service_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def message(self):
+        return lib().kb_service_last_message(self._h).decode()
+
+    def get_suggestions(self, request_bytes):
+        """-> (grpc status code, reply bytes, status message)"""
+        reply, n = C.c_void_p(), C.c_size_t()
+        code = lib().kb_service_get_suggestions(self._h, request_bytes, len(request_bytes), C.byref(reply), C.byref(n))
+        data = C.string_at(reply, n.value) if n.value else b""
+        return code, data, self.message()
+
+    def validate(self, request_bytes):
+        """-> (grpc status code, status message); request_bytes None = nil request"""
+        code = lib().kb_service_validate_algorithm_settings(self._h, request_bytes, len(request_bytes) if request_bytes else 0)
+        return code, self.message()
 
 
 class Context:
@@ -283,6 +326,11 @@ class Context:
         w, V = np.zeros(n), np.zeros((n, n))
         self._ck(lib().kb_eigh(self._h, n, _ptr(A), _ptr(w), _ptr(V)))
         return w, V
+
+    def eigh_sweeps(self):
+        v = C.c_int()
+        self._ck(lib().kb_eigh_stats(self._h, C.byref(v)))
+        return v.value
 
     def random_fill(self, seed, first, n):
         out = np.zeros((n, self.D))

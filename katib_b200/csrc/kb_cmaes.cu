@@ -25,7 +25,9 @@ struct KbCma {
     int n = 0, lam = 0, mu = 0, g = 0;
     double mu_eff, c1, cmu, c_sigma, d_sigma, cc, chi_n, cm, sum_w;
     double sigma = 0;
-    bool have_eig = false, bounded = false;
+    bool have_eig = false, bounded = false, have_bt = false;
+    int last_sweeps = 0;
+    double *d_Bt = nullptr;
     int cap = 0;  // rows the batch buffers hold (>= lam)
     std::vector<double> h_w;
     double *d_mean = nullptr, *d_C = nullptr, *d_ps = nullptr, *d_pc = nullptr, *d_B = nullptr, *d_D = nullptr,
@@ -41,7 +43,7 @@ static void cma_free(KbCma *c) {
     double *ptrs[] = {c->d_mean, c->d_C, c->d_ps, c->d_pc, c->d_B, c->d_D, c->d_Dinv, c->d_D2, c->d_lam, c->d_C2, c->d_w,
                       c->d_wio, c->d_yw, c->d_c2yw, c->d_lo, c->d_hi, c->d_scal, c->d_X, c->d_Xt, c->d_Y, c->d_Yt, c->d_V, c->d_Z};
     for (double *p : ptrs) cudaFree(p);
-    cudaFree(c->d_perm); cudaFree(c->d_flag); cudaFree(c->d_count); cudaFree(c->d_eigws);
+    cudaFree(c->d_perm); cudaFree(c->d_flag); cudaFree(c->d_count); cudaFree(c->d_eigws); cudaFree(c->d_Bt);
     delete c;
 }
 int kb_cmaes_free(kb_ctx *ctx) {
@@ -237,7 +239,7 @@ extern "C" int kb_cmaes_create(kb_ctx *ctx, int n, const double *mean, double si
     CMA_ALLOC(c->d_mean, n); CMA_ALLOC(c->d_C, nn); CMA_ALLOC(c->d_ps, n); CMA_ALLOC(c->d_pc, n); CMA_ALLOC(c->d_B, nn);
     CMA_ALLOC(c->d_D, n); CMA_ALLOC(c->d_Dinv, n); CMA_ALLOC(c->d_D2, n); CMA_ALLOC(c->d_lam, n); CMA_ALLOC(c->d_C2, nn);
     CMA_ALLOC(c->d_w, lam); CMA_ALLOC(c->d_wio, lam); CMA_ALLOC(c->d_yw, n); CMA_ALLOC(c->d_c2yw, n); CMA_ALLOC(c->d_scal, 8);
-    CMA_ALLOC(c->d_count, 1);
+    CMA_ALLOC(c->d_count, 1); CMA_ALLOC(c->d_Bt, nn);
     KB_CUDA(ctx, cudaMalloc(&c->d_eigws, kb_eigh_workspace_bytes(n)));
     if (c->bounded) {
         CMA_ALLOC(c->d_lo, n); CMA_ALLOC(c->d_hi, n);
@@ -259,8 +261,11 @@ extern "C" int kb_cmaes_create(kb_ctx *ctx, int n, const double *mean, double si
 static int cma_ensure_eig(kb_ctx *ctx, KbCma *c, cudaStream_t s) {
     if (c->have_eig) return KB_OK;
     const int n = c->n;
-    int rc = kb_eigh_device(ctx, n, c->d_C, 0.0, c->d_lam, c->d_B, c->d_eigws, s);
+    // warm start from the previous generation's eigenvectors (d_Bt holds B^T once a factorisation exists)
+    int rc = kb_eigh_device(ctx, n, c->d_C, 0.0, c->d_lam, c->d_B, c->d_eigws, s, c->have_bt ? c->d_Bt : nullptr, &c->last_sweeps);
     if (rc) return rc;
+    if ((rc = kb_transpose(ctx, n, n, c->d_B, c->d_Bt, s))) return rc;
+    c->have_bt = true;
     cma_d_from_lambda_kernel<<<(n + 127) / 128, 128, 0, s>>>(n, c->d_lam, c->d_D, c->d_Dinv, c->d_D2);
     KB_LAUNCH_CHECK(ctx);
     // C <- B D^2 B^T (the reference rebuilds C from its factors)

@@ -129,6 +129,7 @@ struct kb_ctx {
 
     KbComm *comm = nullptr;
     KbCma *cma = nullptr;
+    int last_eigh_sweeps = 0;        // Jacobi sweeps of the most recent factorisation (kb_eigh_stats)
 
     // per-kernel-class CUDA-event timing (kb_profile / kb_profile_read); off by default
     bool profile = false;

@@ -196,6 +196,110 @@ jacobi_onesided_kernel(int n, double *Gt, double *Vt, EighShared *sh, double tol
     }
 }
 
+// ---- the multi-CTA solver: one CTA per column pair, data-flow synchronisation instead of a grid barrier ---------
+// In round-robin order the pair (p, q) of step t only needs the two pairs of step t-1 that held p and q.  Every
+// column carries a counter of completed steps (release store after the CTA's writes, acquire poll before the next
+// CTA reads), so a step costs one L2 round trip instead of a grid-wide barrier; the grid synchronises once per sweep
+// to agree on convergence.  Cooperative launch guarantees that all CTAs are resident, which the polling needs.
+#define EF_THREADS 128
+#define EF_NPT 8  // rows per thread held in registers when n <= EF_THREADS * EF_NPT
+
+__device__ __forceinline__ int ld_acquire_gpu(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(int *p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(EF_THREADS)
+jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, int *sweep_rot, double tol) {
+    __shared__ double s_red[3][EF_THREADS / 32];
+    const int N = n + (n & 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool cached = n <= EF_THREADS * EF_NPT;
+    cg::grid_group grid = cg::this_grid();
+    int t = 0;  // global step counter across sweeps
+    for (int sweep = 0; sweep < EG_MAX_SWEEPS; sweep++) {
+        int my_rot = 0;
+        for (int r = 0; r < N - 1; r++, t++) {
+            for (int i = blockIdx.x; i < N / 2; i += gridDim.x) {
+                int p, q;
+                rr_pair(N, r, i, p, q);
+                if (tid == 0) {
+                    while (ld_acquire_gpu(&colstep[p]) < t) {}
+                    while (ld_acquire_gpu(&colstep[q]) < t) {}
+                }
+                __syncthreads();
+                if (q < n) {
+                    double *gp = Gt + (size_t)p * n, *gq = Gt + (size_t)q * n;
+                    double x[EF_NPT], y[EF_NPT];
+                    double a = 0.0, b = 0.0, c = 0.0;
+                    if (cached) {
+#pragma unroll
+                        for (int e = 0; e < EF_NPT; e++) {
+                            const int k = tid + e * EF_THREADS;
+                            x[e] = k < n ? __ldcg(gp + k) : 0.0;
+                            y[e] = k < n ? __ldcg(gq + k) : 0.0;
+                        }
+#pragma unroll
+                        for (int e = 0; e < EF_NPT; e++) { a += x[e] * x[e]; b += y[e] * y[e]; c += x[e] * y[e]; }
+                    } else {
+                        for (int k = tid; k < n; k += EF_THREADS) {
+                            const double xv = __ldcg(gp + k), yv = __ldcg(gq + k);
+                            a += xv * xv; b += yv * yv; c += xv * yv;
+                        }
+                    }
+                    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+                    if (lane == 0) { s_red[0][warp] = a; s_red[1][warp] = b; s_red[2][warp] = c; }
+                    __syncthreads();
+                    a = b = c = 0.0;
+#pragma unroll
+                    for (int w2 = 0; w2 < EF_THREADS / 32; w2++) { a += s_red[0][w2]; b += s_red[1][w2]; c += s_red[2][w2]; }
+                    if (!(fabs(c) <= tol * sqrt(a * b) || c == 0.0)) {  // block-uniform
+                        const double zeta = (b - a) / (2.0 * c);
+                        const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                        const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+                        double *vp = Vt + (size_t)p * n, *vq = Vt + (size_t)q * n;
+                        if (cached) {
+#pragma unroll
+                            for (int e = 0; e < EF_NPT; e++) {
+                                const int k = tid + e * EF_THREADS;
+                                if (k < n) {
+                                    __stcg(gp + k, cs * x[e] - sn * y[e]);
+                                    __stcg(gq + k, sn * x[e] + cs * y[e]);
+                                    const double u = __ldcg(vp + k), v = __ldcg(vq + k);
+                                    __stcg(vp + k, cs * u - sn * v);
+                                    __stcg(vq + k, sn * u + cs * v);
+                                }
+                            }
+                        } else {
+                            for (int k = tid; k < n; k += EF_THREADS) {
+                                const double xv = __ldcg(gp + k), yv = __ldcg(gq + k);
+                                __stcg(gp + k, cs * xv - sn * yv);
+                                __stcg(gq + k, sn * xv + cs * yv);
+                                const double u = __ldcg(vp + k), v = __ldcg(vq + k);
+                                __stcg(vp + k, cs * u - sn * v);
+                                __stcg(vq + k, sn * u + cs * v);
+                            }
+                        }
+                        my_rot++;
+                    }
+                    __threadfence();
+                }
+                __syncthreads();
+                if (tid == 0) { st_release_gpu(&colstep[p], t + 1); st_release_gpu(&colstep[q], t + 1); }
+            }
+        }
+        if (tid == 0 && my_rot) atomicAdd(&sweep_rot[sweep], my_rot);
+        grid.sync();
+        const int rot = __ldcg(&sweep_rot[sweep]);
+        if (blockIdx.x == 0 && tid == 0) sh->sweeps = sweep + 1;
+        if (rot == 0) break;
+    }
+}
+
 // lambda_j = v_j . g_j (keeps the sign for indefinite input), then rank by value, canonical signs, write outputs:
 //   w[rank] = lambda, V[i*n + rank] = +-v_j[i]  (row-major, eigenvector `rank` in column `rank`)
 __global__ void eigh_finish_kernel(int n, const double *__restrict__ Gt, const double *__restrict__ Vt, double shift,
@@ -228,26 +332,41 @@ __global__ void eigh_order_kernel(int n, const double *__restrict__ Vt, const do
     for (int k = threadIdx.x; k < n; k += blockDim.x) V[(size_t)k * n + r] = sg * Vt[(size_t)j * n + k];
 }
 
-__global__ void eigh_init_kernel(int n, const double *__restrict__ A, double shift, double *Gt, double *Vt, EighShared *sh) {
+__global__ void eigh_init_kernel(int n, const double *__restrict__ A, double shift, double *Gt, double *Vt, EighShared *sh,
+                                 int *colstep, int *sweep_rot, int warm) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx == 0) { sh->rotated = 0; sh->sweeps = 0; }
-    if (idx >= (size_t)n * n) return;
+    if (idx < (size_t)n + 2) colstep[idx] = 0;
+    if (idx < EG_MAX_SWEEPS) sweep_rot[idx] = 0;
+    if (idx >= (size_t)n * n || warm) return;
     const int j = (int)(idx / n), i = (int)(idx % n);
     // symmetrise as the reference does before factorising: (C + C^T) / 2
     Gt[idx] = 0.5 * (A[(size_t)i * n + j] + A[(size_t)j * n + i]) + (i == j ? shift : 0.0);
     Vt[idx] = i == j ? 1.0 : 0.0;
 }
 
-// workspace: Gt, Vt (n*n each), lam (n), EighShared
-size_t kb_eigh_workspace_bytes(int n) { return sizeof(double) * ((size_t)2 * n * n + n) + 256; }
+// workspace: Gt, Vt (n*n each), lam (n), EighShared, per-column step counters, per-sweep rotation counts
+size_t kb_eigh_workspace_bytes(int n) {
+    return sizeof(double) * ((size_t)2 * n * n + n + 2) + sizeof(int) * ((size_t)n + 4 + EG_MAX_SWEEPS) + 256;
+}
 
+// d_V0t (optional): transposed eigenvectors of a nearby matrix (row j = vector j).  The iteration then starts from
+// G = A V0, V = V0, whose columns are already almost orthogonal -- CMA-ES changes C by a few percent per generation,
+// so the warm start converges in 2-3 sweeps instead of ~10.
 int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *d_w, double *d_V, void *workspace,
-                   cudaStream_t st) {
+                   cudaStream_t st, const double *d_V0t, int *sweeps_out) {
     double *Gt = (double *)workspace, *Vt = Gt + (size_t)n * n, *lam = Vt + (size_t)n * n;
     EighShared *sh = (EighShared *)(lam + n + (n & 1));
+    int *colstep = (int *)(sh + 1), *sweep_rot = colstep + n + 2 + (n & 1);
     KbProf pf(ctx, 9, st);
-    eigh_init_kernel<<<(unsigned)(((size_t)n * n + 255) / 256), 256, 0, st>>>(n, d_A, shift, Gt, Vt, sh);
+    const int warm = d_V0t != nullptr && shift == 0.0;
+    eigh_init_kernel<<<(unsigned)(((size_t)n * n + 255) / 256), 256, 0, st>>>(n, d_A, shift, Gt, Vt, sh, colstep, sweep_rot, warm);
     KB_LAUNCH_CHECK(ctx);
+    if (warm) {
+        KB_CUDA(ctx, cudaMemcpyAsync(Vt, d_V0t, sizeof(double) * (size_t)n * n, cudaMemcpyDeviceToDevice, st));
+        int rc = kb_dgemm_nt(ctx, n, n, n, d_V0t, n, nullptr, d_A, n, Gt, n, 1.0, 0.0, st);  // Gt[j,:] = A v_j
+        if (rc) return rc;
+    }
     const double tol = sqrt((double)n) * 2.220446049250313e-16;  // LAPACK dgesvj-style stopping criterion
     const int pairs = (n + 1) / 2;
     const int warps_per_block = EG_THREADS / 32;
@@ -255,20 +374,21 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
         jacobi_onesided_kernel<false><<<1, EG_THREADS, 0, st>>>(n, Gt, Vt, sh, tol);
         KB_LAUNCH_CHECK(ctx);
     } else {
-        int blocks = (pairs + warps_per_block - 1) / warps_per_block;
-        int per_sm = 0;
-        KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_onesided_kernel<true>, EG_THREADS, 0));
+        int blocks = pairs, per_sm = 0;
+        KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_flag_kernel, EF_THREADS, 0));
         const int cap = per_sm * ctx->prop.multiProcessorCount;
         if (blocks > cap) blocks = cap;
         double tolv = tol;
-        void *args[] = {&n, &Gt, &Vt, &sh, &tolv};
-        KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_onesided_kernel<true>, dim3((unsigned)blocks), dim3(EG_THREADS), args, 0, st));
+        void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv};
+        KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_flag_kernel, dim3((unsigned)blocks), dim3(EF_THREADS), args, 0, st));
         ctx->launches++;
     }
     eigh_finish_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(n, Gt, Vt, shift, lam, d_w, d_V);
     KB_LAUNCH_CHECK(ctx);
     eigh_order_kernel<<<(unsigned)n, 128, 0, st>>>(n, Vt, lam, d_w, d_V);
     KB_LAUNCH_CHECK(ctx);
+    KB_CUDA(ctx, cudaMemcpyAsync(&ctx->last_eigh_sweeps, &sh->sweeps, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (sweeps_out) KB_CUDA(ctx, cudaMemcpyAsync(sweeps_out, &sh->sweeps, sizeof(int), cudaMemcpyDeviceToHost, st));
     return KB_OK;
 }
 
@@ -295,7 +415,7 @@ extern "C" int kb_eigh(kb_ctx *ctx, int n, const double *A, double *w, double *V
     double *d_A = d, *d_V = d + nn, *d_w = d_V + nn;
     void *ws = (void *)(d_w + n + (n & 1));
     cudaError_t e = cudaMemcpyAsync(d_A, A, sizeof(double) * nn, cudaMemcpyHostToDevice, s);
-    int rc = e == cudaSuccess ? kb_eigh_device(ctx, n, d_A, shift, d_w, d_V, ws, s) : kb_fail(ctx, KB_ERR_CUDA, "kb_eigh: H2D");
+    int rc = e == cudaSuccess ? kb_eigh_device(ctx, n, d_A, shift, d_w, d_V, ws, s, nullptr, nullptr) : kb_fail(ctx, KB_ERR_CUDA, "kb_eigh: H2D");
     if (!rc) {
         e = cudaMemcpyAsync(w, d_w, sizeof(double) * n, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess) e = cudaMemcpyAsync(V, d_V, sizeof(double) * nn, cudaMemcpyDeviceToHost, s);
@@ -304,4 +424,10 @@ extern "C" int kb_eigh(kb_ctx *ctx, int n, const double *A, double *w, double *V
     }
     cudaFree(d);
     return rc;
+}
+
+extern "C" int kb_eigh_stats(const kb_ctx *ctx, int *sweeps) {
+    if (!ctx || !sweeps) return KB_ERR_INVALID;
+    *sweeps = ctx->last_eigh_sweeps;
+    return KB_OK;
 }

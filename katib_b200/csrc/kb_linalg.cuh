@@ -9,5 +9,6 @@ int kb_transpose(kb_ctx *ctx, int rows, int cols, const double *in, double *out,
 // symmetric eigendecomposition of (A + A^T)/2 + shift*I; w ascending (shift removed), V[i*n+j] = component i of
 // eigenvector j, canonical signs; workspace of kb_eigh_workspace_bytes(n) bytes
 size_t kb_eigh_workspace_bytes(int n);
+// d_V0t (optional): warm start, transposed eigenvectors of a nearby matrix; sweeps_out (optional, host): sweeps used
 int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *d_w, double *d_V, void *workspace,
-                   cudaStream_t st);
+                   cudaStream_t st, const double *d_V0t, int *sweeps_out);

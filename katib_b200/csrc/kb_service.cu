@@ -1,0 +1,668 @@
+// kb_service.cu -- host-side mirror of Katib's goptuna suggestion service (plain C++; no device code in this file).
+//
+// The reference service is Go (pkg/suggestion/v1beta1/goptuna); Go is not available in this image, so the service
+// logic that sits above the C ABI is written here in C++, function for function, and speaks the same wire format:
+// requests and replies cross kb_service_* as serialized protobuf (pkg/apis/manager/v1beta1/api.proto), which is what
+// a 30-line Go main or any gRPC front end hands over unchanged.
+//
+//   SuggestionService.GetSuggestions              service.go:54-93      -> Service::GetSuggestions
+//   initStudyAndSearchSpaceAtFirstRun             service.go:153-171    -> Service::InitAtFirstRun
+//   syncTrials                                    service.go:96-151     -> Service::SyncTrials
+//   ValidateAlgorithmSettings                     service.go:173-211    -> Service::Validate
+//   toGoptunaSampler                              converter.go:38-108   -> ParseAlgorithm
+//   toGoptunaSearchSpace                          converter.go:110-184  -> ParseSearchSpace
+//   toGoptunaState / getFinalMetric / toGoptunaTrials / toGoptunaParams   converter.go:186-343 -> ConvertTrials
+//   sampleNextParam                               sample.go:28-95       -> Service::SampleNext
+//   findGoptunaTrialIDByParam                     sample.go:97-127      -> Service::FindTrialByParams
+// gRPC codes used by the reference on this path: OK = 0, InvalidArgument = 3, Internal = 13.
+#include <algorithm>
+#include <charconv>
+#include <cmath>
+#include <cstdlib>
+#include <map>
+#include <set>
+
+#include "kb_internal.cuh"
+
+enum { GRPC_OK = 0, GRPC_INVALID_ARGUMENT = 3, GRPC_INTERNAL = 13 };
+
+// ---------------------------------------------------------------------------------------------------------------
+// minimal protobuf wire reader / writer (varint, 64-bit, length-delimited, 32-bit)
+// ---------------------------------------------------------------------------------------------------------------
+struct PbReader {
+    const uint8_t *p, *end;
+    bool ok = true;
+    PbReader(const void *d, size_t n) : p((const uint8_t *)d), end((const uint8_t *)d + n) {}
+    bool done() const { return p >= end || !ok; }
+    uint64_t varint() {
+        uint64_t v = 0;
+        for (int shift = 0; shift < 64 && p < end; shift += 7) {
+            uint8_t b = *p++;
+            v |= (uint64_t)(b & 0x7F) << shift;
+            if (!(b & 0x80)) return v;
+        }
+        ok = false;
+        return 0;
+    }
+    // returns field number, sets wire type; for length-delimited sets sub-span
+    int next(int &wt, PbReader *sub, uint64_t *val) {
+        uint64_t key = varint();
+        if (!ok) return 0;
+        wt = (int)(key & 7);
+        const int field = (int)(key >> 3);
+        switch (wt) {
+            case 0: { uint64_t v = varint(); if (val) *val = v; break; }
+            case 1: { if (end - p < 8) { ok = false; return 0; } uint64_t v; memcpy(&v, p, 8); p += 8; if (val) *val = v; break; }
+            case 2: {
+                uint64_t n = varint();
+                if (!ok || (uint64_t)(end - p) < n) { ok = false; return 0; }
+                if (sub) *sub = PbReader(p, (size_t)n);
+                p += n;
+                break;
+            }
+            case 5: { if (end - p < 4) { ok = false; return 0; } uint32_t v; memcpy(&v, p, 4); p += 4; if (val) *val = v; break; }
+            default: ok = false; return 0;
+        }
+        return field;
+    }
+    std::string str() const { return std::string((const char *)p, (size_t)(end - p)); }
+};
+struct PbWriter {
+    std::string out;
+    void varint(uint64_t v) { while (v >= 0x80) { out.push_back((char)(v | 0x80)); v >>= 7; } out.push_back((char)v); }
+    void bytes(int field, const std::string &s) { varint(((uint64_t)field << 3) | 2); varint(s.size()); out += s; }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// messages (only the fields this path reads)
+// ---------------------------------------------------------------------------------------------------------------
+struct KV { std::string name, value; };
+struct ParameterSpecMsg { std::string name; int type = 0; std::string max, min, step; std::vector<std::string> list; };
+struct ExperimentMsg {
+    std::string name, algorithm_name, objective_metric_name;
+    std::vector<KV> settings;
+    int objective_type = 0;
+    std::vector<ParameterSpecMsg> params;
+    bool has_spec = false;
+};
+struct TrialMsg {
+    std::string name, start_time, completion_time;
+    int condition = 0;
+    std::vector<KV> assignments, metrics;
+};
+struct GetSuggestionsRequestMsg { ExperimentMsg experiment; std::vector<TrialMsg> trials; int current_request_number = 0, total_request_number = 0; };
+
+static KV parse_kv(PbReader r) {
+    KV kv; int wt; PbReader sub(nullptr, 0);
+    while (!r.done()) { int f = r.next(wt, &sub, nullptr); if (f == 1 && wt == 2) kv.name = sub.str(); else if (f == 2 && wt == 2) kv.value = sub.str(); }
+    return kv;
+}
+static ParameterSpecMsg parse_param(PbReader r) {
+    ParameterSpecMsg ps; int wt; PbReader sub(nullptr, 0); uint64_t v;
+    while (!r.done()) {
+        int f = r.next(wt, &sub, &v);
+        if (f == 1 && wt == 2) ps.name = sub.str();
+        else if (f == 2 && wt == 0) ps.type = (int)v;
+        else if (f == 3 && wt == 2) {
+            PbReader fs = sub; PbReader s2(nullptr, 0); int w2;
+            while (!fs.done()) {
+                int g = fs.next(w2, &s2, nullptr);
+                if (w2 != 2) continue;
+                if (g == 1) ps.max = s2.str(); else if (g == 2) ps.min = s2.str(); else if (g == 3) ps.list.push_back(s2.str()); else if (g == 4) ps.step = s2.str();
+            }
+        }
+    }
+    return ps;
+}
+static ExperimentMsg parse_experiment(PbReader r) {
+    ExperimentMsg e; int wt; PbReader sub(nullptr, 0); uint64_t v;
+    while (!r.done()) {
+        int f = r.next(wt, &sub, &v);
+        if (f == 1 && wt == 2) e.name = sub.str();
+        else if (f == 2 && wt == 2) {  // ExperimentSpec
+            e.has_spec = true;
+            PbReader spec = sub; PbReader s2(nullptr, 0); int w2; uint64_t v2;
+            while (!spec.done()) {
+                int g = spec.next(w2, &s2, &v2);
+                if (g == 1 && w2 == 2) {  // ParameterSpecs
+                    PbReader pss = s2; PbReader s3(nullptr, 0); int w3;
+                    while (!pss.done()) { int h = pss.next(w3, &s3, nullptr); if (h == 1 && w3 == 2) e.params.push_back(parse_param(s3)); }
+                } else if (g == 2 && w2 == 2) {  // ObjectiveSpec
+                    PbReader o = s2; PbReader s3(nullptr, 0); int w3; uint64_t v3;
+                    while (!o.done()) { int h = o.next(w3, &s3, &v3); if (h == 1 && w3 == 0) e.objective_type = (int)v3; else if (h == 3 && w3 == 2) e.objective_metric_name = s3.str(); }
+                } else if (g == 3 && w2 == 2) {  // AlgorithmSpec
+                    PbReader a = s2; PbReader s3(nullptr, 0); int w3;
+                    while (!a.done()) { int h = a.next(w3, &s3, nullptr); if (h == 1 && w3 == 2) e.algorithm_name = s3.str(); else if (h == 2 && w3 == 2) e.settings.push_back(parse_kv(s3)); }
+                }
+            }
+        }
+    }
+    return e;
+}
+static TrialMsg parse_trial(PbReader r) {
+    TrialMsg t; int wt; PbReader sub(nullptr, 0);
+    while (!r.done()) {
+        int f = r.next(wt, &sub, nullptr);
+        if (f == 1 && wt == 2) t.name = sub.str();
+        else if (f == 2 && wt == 2) {  // TrialSpec
+            PbReader spec = sub; PbReader s2(nullptr, 0); int w2;
+            while (!spec.done()) {
+                int g = spec.next(w2, &s2, nullptr);
+                if (g == 3 && w2 == 2) {
+                    PbReader pa = s2; PbReader s3(nullptr, 0); int w3;
+                    while (!pa.done()) { int h = pa.next(w3, &s3, nullptr); if (h == 1 && w3 == 2) t.assignments.push_back(parse_kv(s3)); }
+                }
+            }
+        } else if (f == 3 && wt == 2) {  // TrialStatus
+            PbReader st = sub; PbReader s2(nullptr, 0); int w2; uint64_t v2;
+            while (!st.done()) {
+                int g = st.next(w2, &s2, &v2);
+                if (g == 1 && w2 == 2) t.start_time = s2.str();
+                else if (g == 2 && w2 == 2) t.completion_time = s2.str();
+                else if (g == 3 && w2 == 0) t.condition = (int)v2;
+                else if (g == 4 && w2 == 2) {
+                    PbReader ob = s2; PbReader s3(nullptr, 0); int w3;
+                    while (!ob.done()) { int h = ob.next(w3, &s3, nullptr); if (h == 1 && w3 == 2) t.metrics.push_back(parse_kv(s3)); }
+                }
+            }
+        }
+    }
+    return t;
+}
+static bool parse_request(const void *data, size_t n, GetSuggestionsRequestMsg &req) {
+    PbReader r(data, n); int wt; PbReader sub(nullptr, 0); uint64_t v;
+    while (!r.done()) {
+        int f = r.next(wt, &sub, &v);
+        if (f == 1 && wt == 2) req.experiment = parse_experiment(sub);
+        else if (f == 2 && wt == 2) req.trials.push_back(parse_trial(sub));
+        else if (f == 4 && wt == 0) req.current_request_number = (int)(int32_t)v;
+        else if (f == 5 && wt == 0) req.total_request_number = (int)(int32_t)v;
+    }
+    return r.ok;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Go strconv look-alikes
+// ---------------------------------------------------------------------------------------------------------------
+static bool go_atoi(const std::string &s, long long &out, std::string &err) {
+    const char *b = s.c_str(); char *e = nullptr;
+    errno = 0;
+    if (s.empty() || isspace((unsigned char)s[0])) { err = "strconv.Atoi: parsing \"" + s + "\": invalid syntax"; return false; }
+    long long v = strtoll(b, &e, 10);
+    if (e == b || *e != 0 || errno == ERANGE) { err = "strconv.Atoi: parsing \"" + s + "\": invalid syntax"; return false; }
+    out = v;
+    return true;
+}
+static bool go_parse_float(const std::string &s, double &out, std::string &err) {
+    const char *b = s.c_str(); char *e = nullptr;
+    if (s.empty() || isspace((unsigned char)s[0])) { err = "strconv.ParseFloat: parsing \"" + s + "\": invalid syntax"; return false; }
+    double v = strtod(b, &e);
+    if (e == b || *e != 0) { err = "strconv.ParseFloat: parsing \"" + s + "\": invalid syntax"; return false; }
+    out = v;
+    return true;
+}
+// strconv.FormatFloat(p, 'f', -1, 64): shortest digits that round-trip, fixed notation
+static std::string go_format_float(double v) {
+    char buf[512];
+    auto r = std::to_chars(buf, buf + sizeof buf, v, std::chars_format::fixed);
+    return std::string(buf, r.ptr);
+}
+// time.Parse(time.RFC3339Nano, s): YYYY-MM-DDTHH:MM:SS[.frac](Z|+HH:MM|-HH:MM)
+static bool rfc3339_ok(const std::string &s) {
+    auto dig = [&](size_t i) { return i < s.size() && isdigit((unsigned char)s[i]); };
+    if (s.size() < 20) return false;
+    for (size_t i : {0u, 1u, 2u, 3u, 5u, 6u, 8u, 9u, 11u, 12u, 14u, 15u, 17u, 18u}) if (!dig(i)) return false;
+    if (s[4] != '-' || s[7] != '-' || (s[10] != 'T') || s[13] != ':' || s[16] != ':') return false;
+    size_t i = 19;
+    if (s[i] == '.') { i++; size_t j = i; while (dig(i)) i++; if (i == j) return false; }
+    if (i >= s.size()) return false;
+    if (s[i] == 'Z') return i + 1 == s.size();
+    if (s[i] != '+' && s[i] != '-') return false;
+    return i + 6 == s.size() && dig(i + 1) && dig(i + 2) && s[i + 3] == ':' && dig(i + 4) && dig(i + 5);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// the service
+// ---------------------------------------------------------------------------------------------------------------
+enum TrialState { ST_RUNNING = 0, ST_COMPLETE = 1, ST_PRUNED = 2, ST_FAIL = 3 };
+static bool finished(int st) { return st != ST_RUNNING; }
+
+struct Param {  // one entry of the search space
+    std::string name;
+    int kind = KB_UNIFORM;
+    double low = 0, high = 0, step = 0;
+    std::vector<std::string> choices;
+};
+struct Algo {
+    std::string name;
+    long long seed = 0; bool has_seed = false;
+    double sigma = 0; bool has_sigma = false;
+    std::string restart = "none";
+    long long n_startup = 10, n_ei = 24;
+};
+struct InternalTrial {
+    int id = 0, state = ST_RUNNING;
+    double value = 0;
+    std::map<std::string, double> params;  // internal representation by parameter name
+    int cma_generation = -1;
+    bool cma_told = false;
+};
+struct ConvertedTrial { std::string name; int state = ST_RUNNING; double value = 0; std::map<std::string, double> params; };
+
+struct Status { int code = GRPC_OK; std::string msg; };
+static Status fail(int code, const std::string &m) { Status s; s.code = code; s.msg = m; return s; }
+
+struct kb_service {
+    std::mutex mu;
+    int device = 0;
+    kb_ctx *ctx = nullptr;
+    bool initialised = false;
+    Algo algo;
+    std::vector<Param> space;
+    bool maximize = false;
+    std::vector<InternalTrial> trials;
+    std::map<std::string, int> mapping;  // Katib trial name -> internal trial id
+    bool history_dirty = true;
+    uint64_t draw_counter = 0;
+    // cmaes
+    bool cma_ready = false;
+    std::vector<int> cma_dims;  // indices into space of the numeric parameters, sorted by name
+    int cma_generation = 0, cma_popsize = 0;
+    std::string last_message;
+    std::string reply;
+};
+
+static const char *kFailedStudy = "Failed to create goptuna study and search space: ";
+
+// toGoptunaSampler (converter.go:38-108): settings are parsed, unknown names ignored
+static bool ParseAlgorithm(const ExperimentMsg &e, Algo &a, std::string &err) {
+    a = Algo();
+    a.name = e.algorithm_name;
+    for (const KV &s : e.settings) {
+        if (a.name == "cmaes") {
+            if (s.name == "random_state") { if (!go_atoi(s.value, a.seed, err)) return false; a.has_seed = true; }
+            else if (s.name == "sigma") { if (!go_parse_float(s.value, a.sigma, err)) return false; a.has_sigma = true; }
+            else if (s.name == "restart_strategy") {
+                if (s.value == "ipop" || s.value == "bipop" || s.value == "none") a.restart = s.value;
+                else { err = "invalid restart_strategy: '" + s.value + "'"; return false; }
+            }
+        } else if (a.name == "tpe") {
+            if (s.name == "random_state") { if (!go_atoi(s.value, a.seed, err)) return false; a.has_seed = true; }
+            else if (s.name == "n_startup_trials") { if (!go_atoi(s.value, a.n_startup, err)) return false; }
+            else if (s.name == "n_ei_candidates") { if (!go_atoi(s.value, a.n_ei, err)) return false; }
+        } else if (a.name != "sobol") {
+            if (s.name == "random_state") { if (!go_atoi(s.value, a.seed, err)) return false; a.has_seed = true; }
+        }
+    }
+    return true;
+}
+
+// toGoptunaSearchSpace (converter.go:110-184)
+static bool ParseSearchSpace(const ExperimentMsg &e, std::vector<Param> &space, std::string &err) {
+    space.clear();
+    for (const ParameterSpecMsg &p : e.params) {
+        Param q; q.name = p.name;
+        if (p.type == 1) {  // DOUBLE
+            if (!go_parse_float(p.max, q.high, err) || !go_parse_float(p.min, q.low, err)) return false;
+            if (p.step.empty()) q.kind = KB_UNIFORM;
+            else { if (!go_parse_float(p.step, q.step, err)) return false; q.kind = KB_DISCRETE; }
+        } else if (p.type == 2) {  // INT
+            long long hi, lo, st;
+            if (!go_atoi(p.max, hi, err) || !go_atoi(p.min, lo, err)) return false;
+            q.high = (double)hi; q.low = (double)lo;
+            if (p.step.empty()) q.kind = KB_INT;
+            else { if (!go_atoi(p.step, st, err)) return false; q.step = (double)st; q.kind = KB_STEP_INT; }
+        } else if (p.type == 4 || p.type == 3) {  // CATEGORICAL, and DISCRETE as categorical (converter.go:166-178)
+            q.kind = KB_CATEGORICAL; q.choices = p.list;
+        } else {
+            err = "Unsupported parameter type: " + std::to_string(p.type);
+            return false;
+        }
+        // a Go map keyed by name: a later duplicate replaces the earlier entry
+        bool replaced = false;
+        for (Param &o : space) if (o.name == q.name) { o = q; replaced = true; }
+        if (!replaced) space.push_back(q);
+    }
+    return true;
+}
+
+static Status Validate(const ExperimentMsg *e) {
+    if (!e) return fail(GRPC_INVALID_ARGUMENT, "request is empty");
+    const std::string &n = e->algorithm_name;
+    if (n != "random" && n != "cmaes" && n != "tpe" && n != "sobol") return fail(GRPC_INVALID_ARGUMENT, "unsupported algorithm");
+    if (n == "cmaes") {
+        int cnt = 0;
+        for (const ParameterSpecMsg &p : e->params) if (p.type == 1 || p.type == 2) cnt++;
+        if (cnt < 2) return fail(GRPC_INVALID_ARGUMENT, "CMA-ES only supports two or more dimensional continuous search space.");
+    }
+    std::set<std::string> seen;
+    for (const ParameterSpecMsg &p : e->params) {
+        if (seen.count(p.name)) return fail(GRPC_INVALID_ARGUMENT, "Detect duplicated parameter name: " + p.name);
+        seen.insert(p.name);
+    }
+    Algo a; std::vector<Param> sp; std::string err;
+    if (!ParseAlgorithm(*e, a, err) || !ParseSearchSpace(*e, sp, err)) return fail(GRPC_INTERNAL, kFailedStudy + err);
+    return Status();
+}
+
+static const Param *find_param(const std::vector<Param> &space, const std::string &name) {
+    for (const Param &p : space) if (p.name == name) return &p;
+    return nullptr;
+}
+
+// toGoptunaTrials + toGoptunaParams + toGoptunaState + getFinalMetric (converter.go:186-343)
+static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &metric, const std::vector<Param> &space,
+                          std::vector<ConvertedTrial> &out, std::string &err) {
+    out.clear();
+    for (const TrialMsg &kt : in) {
+        ConvertedTrial t; t.name = kt.name;
+        if (!kt.start_time.empty() && !rfc3339_ok(kt.start_time)) { err = "parsing time \"" + kt.start_time + "\" as \"2006-01-02T15:04:05.999999999Z07:00\": cannot parse"; return false; }
+        if (!kt.completion_time.empty() && !rfc3339_ok(kt.completion_time)) { err = "parsing time \"" + kt.completion_time + "\" as \"2006-01-02T15:04:05.999999999Z07:00\": cannot parse"; return false; }
+        switch (kt.condition) {
+            case 0: case 1: t.state = ST_RUNNING; break;      // CREATED, RUNNING
+            case 2: t.state = ST_COMPLETE; break;             // SUCCEEDED
+            case 4: t.state = ST_FAIL; break;                 // FAILED
+            case 6: t.state = ST_PRUNED; break;               // EARLYSTOPPED
+            default: err = "Unexpected Trial condition: " + std::to_string(kt.condition); return false;
+        }
+        if (t.state == ST_COMPLETE) {
+            bool found = false;
+            for (size_t i = kt.metrics.size(); i-- > 0;) {
+                if (kt.metrics[i].name != metric) continue;
+                if (!go_parse_float(kt.metrics[i].value, t.value, err)) return false;
+                found = true;
+                break;
+            }
+            if (!found) { err = "No objective metric in Trial " + kt.name; return false; }
+        }
+        for (const KV &a : kt.assignments) {
+            const Param *p = find_param(space, a.name);
+            if (!p) continue;  // a name outside the search space matches no case of the Go type switch
+            double v = 0;
+            if (p->kind == KB_UNIFORM || p->kind == KB_DISCRETE) { if (!go_parse_float(a.value, v, err)) return false; }
+            else if (p->kind == KB_INT || p->kind == KB_STEP_INT) {
+                long long iv;
+                if (!go_atoi(a.value, iv, err)) { err = "strconv.ParseInt: parsing \"" + a.value + "\": invalid syntax"; return false; }
+                v = (double)iv;
+            } else {
+                int idx = -1;
+                for (size_t c = 0; c < p->choices.size(); c++) if (p->choices[c] == a.value) { idx = (int)c; break; }
+                if (idx < 0) { err = "Invalid categorical value: -1"; return false; }
+                v = (double)idx;
+            }
+            t.params[a.name] = v;
+        }
+        // a Go map keyed by trial name: a later duplicate replaces the earlier entry
+        bool replaced = false;
+        for (ConvertedTrial &o : out) if (o.name == t.name) { o = t; replaced = true; }
+        if (!replaced) out.push_back(t);
+    }
+    return true;
+}
+
+// findGoptunaTrialIDByParam (sample.go:97-127): newest unmapped Running trial with identical parameters
+static int FindTrialByParams(kb_service *s, const ConvertedTrial &kt) {
+    std::set<int> mapped;
+    for (auto &m : s->mapping) mapped.insert(m.second);
+    for (size_t i = s->trials.size(); i-- > 0;) {
+        const InternalTrial &t = s->trials[i];
+        if (t.state != ST_RUNNING || mapped.count(t.id)) continue;
+        if (t.params == kt.params) return t.id;
+    }
+    return -1;
+}
+
+static Status SyncTrials(kb_service *s, const std::vector<ConvertedTrial> &kts) {
+    for (const ConvertedTrial &kt : kts) {
+        int id;
+        auto it = s->mapping.find(kt.name);
+        if (it == s->mapping.end()) {
+            id = FindTrialByParams(s, kt);
+            if (id < 0) return fail(GRPC_INTERNAL, "Same parameter is not found for Trial: " + kt.name);
+            s->mapping[kt.name] = id;
+        } else id = it->second;
+        InternalTrial &t = s->trials[(size_t)id];
+        if (finished(t.state)) continue;          // finished trials are never updated
+        if (kt.state == t.state) continue;
+        if (kt.state == ST_COMPLETE) t.value = kt.value;
+        t.state = kt.state;
+        s->history_dirty = true;
+    }
+    return Status();
+}
+
+static Status engine_error(kb_service *s, const char *what) {
+    return fail(GRPC_INTERNAL, std::string(what) + ": " + kb_last_error(s->ctx));
+}
+
+// upload Complete (and value-less Pruned, ranked last) trials as the TPE history
+static Status PushHistory(kb_service *s) {
+    if (!s->history_dirty) return Status();
+    const size_t D = s->space.size();
+    std::vector<double> values, loss;
+    for (const InternalTrial &t : s->trials) {
+        if (t.state != ST_COMPLETE && t.state != ST_PRUNED) continue;
+        bool all = true;
+        for (const Param &p : s->space) if (!t.params.count(p.name)) all = false;
+        if (!all) continue;
+        for (const Param &p : s->space) values.push_back(t.params.at(p.name));
+        loss.push_back(t.state == ST_COMPLETE ? (s->maximize ? -t.value : t.value) : INFINITY);
+    }
+    if (kb_tpe_set_history(s->ctx, (int64_t)loss.size(), values.empty() ? nullptr : values.data(), loss.empty() ? nullptr : loss.data()))
+        return engine_error(s, "kb_tpe_set_history");
+    (void)D;
+    s->history_dirty = false;
+    return Status();
+}
+
+static int n_observations(const kb_service *s) {
+    int n = 0;
+    for (const InternalTrial &t : s->trials) if (t.state == ST_COMPLETE || t.state == ST_PRUNED) n++;
+    return n;
+}
+
+static uint64_t mix_seed(uint64_t seed, uint64_t counter) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (counter + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// map a unit-cube coordinate to a distribution (sobol): uniform affine; integers / grids by floor; categorical by floor
+static double from_unit(const Param &p, double u) {
+    switch (p.kind) {
+        case KB_UNIFORM: return p.low + u * (p.high - p.low);
+        case KB_INT: return std::min(p.high, std::floor(p.low + u * (p.high - p.low + 1.0)));
+        case KB_STEP_INT:
+        case KB_DISCRETE: { const double nq = std::floor((p.high - p.low) / p.step); return p.low + p.step * std::min(nq, std::floor(u * (nq + 1.0))); }
+        default: return std::min((double)p.choices.size() - 1.0, std::floor(u * (double)p.choices.size()));
+    }
+}
+
+static Status CmaStep(kb_service *s, std::vector<double> &x_out) {
+    // cmaes.Sampler.SampleRelative: numeric parameters sorted by name; lazily created optimiser; Tell once popsize
+    // Complete trials of the current generation exist; then Ask one solution
+    if (!s->cma_ready) {
+        s->cma_dims.clear();
+        for (size_t i = 0; i < s->space.size(); i++) if (s->space[i].kind != KB_CATEGORICAL) s->cma_dims.push_back((int)i);
+        std::sort(s->cma_dims.begin(), s->cma_dims.end(), [&](int a, int b) { return s->space[(size_t)a].name < s->space[(size_t)b].name; });
+        const int n = (int)s->cma_dims.size();
+        std::vector<double> mean((size_t)n), lo((size_t)n), hi((size_t)n);
+        double sigma0 = INFINITY;
+        for (int i = 0; i < n; i++) {
+            const Param &p = s->space[(size_t)s->cma_dims[(size_t)i]];
+            lo[(size_t)i] = p.low; hi[(size_t)i] = p.high;
+            mean[(size_t)i] = p.low + (p.high - p.low) / 2.0;
+            sigma0 = std::min(sigma0, (p.high - p.low) / 6.0);
+        }
+        if (s->algo.has_sigma) sigma0 = s->algo.sigma;
+        if (kb_cmaes_create(s->ctx, n, mean.data(), sigma0, 0, lo.data(), hi.data())) return engine_error(s, "kb_cmaes_create");
+        s->cma_popsize = 4 + (int)std::floor(3.0 * std::log((double)n));
+        s->cma_generation = 0;
+        s->cma_ready = true;
+    }
+    const int n = (int)s->cma_dims.size();
+    std::vector<const InternalTrial *> sol;
+    for (const InternalTrial &t : s->trials)
+        if (t.state == ST_COMPLETE && t.cma_generation == s->cma_generation && !t.cma_told) sol.push_back(&t);
+    if ((int)sol.size() >= s->cma_popsize) {
+        std::vector<double> X((size_t)s->cma_popsize * n), f((size_t)s->cma_popsize);
+        for (int k = 0; k < s->cma_popsize; k++) {
+            for (int i = 0; i < n; i++) X[(size_t)k * n + i] = sol[(size_t)k]->params.at(s->space[(size_t)s->cma_dims[(size_t)i]].name);
+            f[(size_t)k] = s->maximize ? -sol[(size_t)k]->value : sol[(size_t)k]->value;
+        }
+        if (kb_cmaes_tell(s->ctx, X.data(), f.data())) return engine_error(s, "kb_cmaes_tell");
+        for (InternalTrial &t : s->trials) if (t.cma_generation == s->cma_generation) t.cma_told = true;
+        s->cma_generation += 1;
+    }
+    x_out.assign((size_t)n, 0.0);
+    const uint64_t seed = mix_seed((uint64_t)s->algo.seed, s->draw_counter++);
+    if (kb_cmaes_ask(s->ctx, 1, nullptr, seed, x_out.data())) return engine_error(s, "kb_cmaes_ask");
+    return Status();
+}
+
+// sampleNextParam (sample.go:28-95)
+static Status SampleNext(kb_service *s, std::vector<KV> &assignments) {
+    InternalTrial t;
+    t.id = (int)s->trials.size();
+    const size_t D = s->space.size();
+    std::vector<double> v(D, 0.0);
+    const std::string &algo = s->algo.name;
+    if (algo == "tpe" && n_observations(s) >= s->algo.n_startup) {
+        Status st = PushHistory(s);
+        if (st.code) return st;
+        if (kb_tpe_suggest(s->ctx, s->algo.n_ei, mix_seed((uint64_t)s->algo.seed, s->draw_counter++), v.data()))
+            return engine_error(s, "kb_tpe_suggest");
+    } else if (algo == "sobol") {
+        std::vector<int> order(D);
+        for (size_t i = 0; i < D; i++) order[i] = (int)i;
+        std::sort(order.begin(), order.end(), [&](int a, int b) { return s->space[(size_t)a].name < s->space[(size_t)b].name; });
+        std::vector<double> u(D);
+        const char *skip = getenv("KB_SOBOL_SKIP_FIRST");
+        const uint64_t index = s->draw_counter++ + (skip && skip[0] == '1' ? 1 : 0);
+        if (kb_sobol_fill(s->ctx, (int)D, index, 1, nullptr, nullptr, u.data())) return engine_error(s, "kb_sobol_fill");
+        for (size_t k = 0; k < D; k++) v[(size_t)order[k]] = from_unit(s->space[(size_t)order[k]], u[k]);
+    } else {
+        // random, TPE's start-up phase, and the independent sampler behind CMA-ES's categorical parameters
+        if (kb_random_fill(s->ctx, (uint64_t)s->algo.seed, s->draw_counter++, 1, v.data())) return engine_error(s, "kb_random_fill");
+        if (algo == "cmaes") {
+            std::vector<double> x;
+            Status st = CmaStep(s, x);
+            if (st.code) return st;
+            for (size_t i = 0; i < s->cma_dims.size(); i++) {
+                const Param &p = s->space[(size_t)s->cma_dims[i]];
+                double xv = x[i];
+                if (p.kind == KB_INT) xv = std::round(xv);
+                else if (p.kind == KB_STEP_INT || p.kind == KB_DISCRETE) xv = std::round((xv - p.low) / p.step) * p.step + p.low;
+                v[(size_t)s->cma_dims[i]] = std::min(std::max(xv, p.low), p.high);
+            }
+            t.cma_generation = s->cma_generation;
+        }
+    }
+    assignments.clear();
+    for (size_t i = 0; i < D; i++) {
+        const Param &p = s->space[i];
+        KV a; a.name = p.name;
+        if (p.kind == KB_UNIFORM || p.kind == KB_DISCRETE) a.value = go_format_float(v[i]);
+        else if (p.kind == KB_INT || p.kind == KB_STEP_INT) a.value = std::to_string((long long)std::llround(v[i]));
+        else {
+            int c = (int)v[i];
+            c = std::max(0, std::min(c, (int)p.choices.size() - 1));
+            a.value = p.choices.empty() ? std::string() : p.choices[(size_t)c];
+            v[i] = (double)c;
+        }
+        if (p.kind == KB_INT || p.kind == KB_STEP_INT) v[i] = (double)std::llround(v[i]);
+        t.params[p.name] = v[i];
+        assignments.push_back(a);
+    }
+    s->trials.push_back(t);
+    return Status();
+}
+
+static Status InitAtFirstRun(kb_service *s, const ExperimentMsg &e) {
+    if (s->initialised) return Status();
+    std::string err;
+    Algo a; std::vector<Param> sp;
+    if (!ParseAlgorithm(e, a, err) || !ParseSearchSpace(e, sp, err)) return fail(GRPC_INTERNAL, kFailedStudy + err);
+    if (sp.empty()) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + "empty search space");
+    if (!s->ctx && kb_create(s->device, &s->ctx)) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(nullptr));
+    const size_t D = sp.size();
+    std::vector<int32_t> kind(D), nch(D);
+    std::vector<double> lo(D), hi(D), st(D);
+    for (size_t i = 0; i < D; i++) { kind[i] = sp[i].kind; lo[i] = sp[i].low; hi[i] = sp[i].high; st[i] = sp[i].step; nch[i] = (int32_t)sp[i].choices.size(); }
+    if (kb_space_set(s->ctx, (int)D, kind.data(), lo.data(), hi.data(), st.data(), nch.data()))
+        return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(s->ctx));
+    s->algo = a; s->space = sp;
+    s->maximize = e.objective_type != 1;  // toGoptunaDirection: MINIMIZE -> minimise, anything else -> maximise
+    s->initialised = true;
+    return Status();
+}
+
+static Status GetSuggestions(kb_service *s, const GetSuggestionsRequestMsg &req, std::string &reply) {
+    Status st = InitAtFirstRun(s, req.experiment);
+    if (st.code) return st;
+    std::vector<ConvertedTrial> kts;
+    std::string err;
+    if (!ConvertTrials(req.trials, req.experiment.objective_metric_name, s->space, kts, err)) return fail(GRPC_INTERNAL, err);
+    st = SyncTrials(s, kts);
+    if (st.code) return st;
+    PbWriter w;
+    for (int i = 0; i < req.current_request_number; i++) {
+        std::vector<KV> as;
+        st = SampleNext(s, as);
+        if (st.code) return st;
+        PbWriter pa;
+        for (const KV &a : as) { PbWriter kv; kv.bytes(1, a.name); kv.bytes(2, a.value); pa.bytes(1, kv.out); }
+        w.bytes(1, pa.out);
+    }
+    reply = w.out;
+    return Status();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" int kb_service_create(int device, kb_service **out) {
+    if (!out) return KB_ERR_INVALID;
+    kb_service *s = new kb_service();
+    s->device = device;
+    *out = s;
+    return KB_OK;
+}
+extern "C" int kb_service_destroy(kb_service *s) {
+    if (!s) return KB_OK;
+    if (s->ctx) kb_destroy(s->ctx);
+    delete s;
+    return KB_OK;
+}
+extern "C" const char *kb_service_last_message(const kb_service *s) { return s ? s->last_message.c_str() : ""; }
+
+extern "C" int kb_service_get_suggestions(kb_service *s, const void *request, size_t request_len, const void **reply,
+                                          size_t *reply_len) {
+    if (!s) return GRPC_INTERNAL;
+    std::lock_guard<std::mutex> lk(s->mu);
+    GetSuggestionsRequestMsg req;
+    Status st;
+    if (!parse_request(request, request_len, req)) st = fail(GRPC_INTERNAL, "malformed GetSuggestionsRequest");
+    else st = GetSuggestions(s, req, s->reply);
+    s->last_message = st.msg;
+    if (st.code) s->reply.clear();
+    if (reply) *reply = s->reply.data();
+    if (reply_len) *reply_len = s->reply.size();
+    return st.code;
+}
+
+extern "C" int kb_service_validate_algorithm_settings(kb_service *s, const void *request, size_t request_len) {
+    if (!s) return GRPC_INTERNAL;
+    std::lock_guard<std::mutex> lk(s->mu);
+    Status st;
+    if (!request) st = Validate(nullptr);
+    else {
+        PbReader r(request, request_len); int wt; PbReader sub(nullptr, 0);
+        ExperimentMsg e;
+        while (!r.done()) { int f = r.next(wt, &sub, nullptr); if (f == 1 && wt == 2) e = parse_experiment(sub); }
+        st = r.ok ? Validate(&e) : fail(GRPC_INTERNAL, "malformed ValidateAlgorithmSettingsRequest");
+    }
+    s->last_message = st.msg;
+    return st.code;
+}
