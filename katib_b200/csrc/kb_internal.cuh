@@ -38,14 +38,19 @@ struct KbDim {
     // quantised parameters, components whose sigma was clipped to the magic-clip floor (nearly all of them once the
     // history is dense): Phi(b)-Phi(a) with the fixed half width h0 is one function of y = |x-mu|/(sqrt2 sigma):
     //   erfc(y-h0) - erfc(y+h0) = 2^( -(y'-h0')^2 + R(tau) ),  y' = sqrt(log2 e) y, tau = y' * qf_tau_s - 1,
-    // R = degree-KB_QF_DEG polynomial fitted per (parameter, side) at build time (Chebyshev-node interpolation).
+    // R = degree-KB_QF_DEG polynomial fitted per (parameter, side) at build time (Chebyshev-node interpolation on
+    // y in [0, KB_QF_YMAX]; beyond it the term is < e^-29 of a component's peak and tau is clamped).
     float qf_coef[2][16];
     float qf_h0[2];           // h0' = sqrt(log2 e) * q / (2 sqrt2 sigma_min)
     float qf_tau_s[2];        // 2 / (sqrt(log2 e) * KB_QF_YMAX)
     float qf_hw[2];           // normalised half bin width q_n / 2 the fit assumes
 };
-#define KB_QF_DEG 12
-#define KB_QF_YMAX 7.5
+#ifndef KB_QF_DEG
+#define KB_QF_DEG 11
+#endif
+#ifndef KB_QF_YMAX
+#define KB_QF_YMAX 6.0
+#endif
 
 #define KB_TABLE_PAD 32
 

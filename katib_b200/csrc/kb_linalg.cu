@@ -234,14 +234,22 @@ jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, 
                 __syncthreads();
                 if (q < n) {
                     double *gp = Gt + (size_t)p * n, *gq = Gt + (size_t)q * n;
-                    double x[EF_NPT], y[EF_NPT];
+                    double *vp = Vt + (size_t)p * n, *vq = Vt + (size_t)q * n;
+                    double x[EF_NPT], y[EF_NPT], u[EF_NPT], v[EF_NPT];
                     double a = 0.0, b = 0.0, c = 0.0;
                     if (cached) {
+                        // all four columns are requested up front: the V loads overlap the reduction and the rotation maths
 #pragma unroll
                         for (int e = 0; e < EF_NPT; e++) {
                             const int k = tid + e * EF_THREADS;
                             x[e] = k < n ? __ldcg(gp + k) : 0.0;
                             y[e] = k < n ? __ldcg(gq + k) : 0.0;
+                        }
+#pragma unroll
+                        for (int e = 0; e < EF_NPT; e++) {
+                            const int k = tid + e * EF_THREADS;
+                            u[e] = k < n ? __ldcg(vp + k) : 0.0;
+                            v[e] = k < n ? __ldcg(vq + k) : 0.0;
                         }
 #pragma unroll
                         for (int e = 0; e < EF_NPT; e++) { a += x[e] * x[e]; b += y[e] * y[e]; c += x[e] * y[e]; }
@@ -260,8 +268,7 @@ jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, 
                     if (!(fabs(c) <= tol * sqrt(a * b) || c == 0.0)) {  // block-uniform
                         const double zeta = (b - a) / (2.0 * c);
                         const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                        const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
-                        double *vp = Vt + (size_t)p * n, *vq = Vt + (size_t)q * n;
+                        const double cs = rsqrt(1.0 + tt * tt), sn = cs * tt;
                         if (cached) {
 #pragma unroll
                             for (int e = 0; e < EF_NPT; e++) {
@@ -269,9 +276,8 @@ jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, 
                                 if (k < n) {
                                     __stcg(gp + k, cs * x[e] - sn * y[e]);
                                     __stcg(gq + k, sn * x[e] + cs * y[e]);
-                                    const double u = __ldcg(vp + k), v = __ldcg(vq + k);
-                                    __stcg(vp + k, cs * u - sn * v);
-                                    __stcg(vq + k, sn * u + cs * v);
+                                    __stcg(vp + k, cs * u[e] - sn * v[e]);
+                                    __stcg(vq + k, sn * u[e] + cs * v[e]);
                                 }
                             }
                         } else {
@@ -279,15 +285,15 @@ jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, 
                                 const double xv = __ldcg(gp + k), yv = __ldcg(gq + k);
                                 __stcg(gp + k, cs * xv - sn * yv);
                                 __stcg(gq + k, sn * xv + cs * yv);
-                                const double u = __ldcg(vp + k), v = __ldcg(vq + k);
-                                __stcg(vp + k, cs * u - sn * v);
-                                __stcg(vq + k, sn * u + cs * v);
+                                const double uu = __ldcg(vp + k), vv = __ldcg(vq + k);
+                                __stcg(vp + k, cs * uu - sn * vv);
+                                __stcg(vq + k, sn * uu + cs * vv);
                             }
                         }
                         my_rot++;
                     }
-                    __threadfence();
                 }
+                // the release store below, issued after the CTA barrier, publishes every thread's writes (cumulativity)
                 __syncthreads();
                 if (tid == 0) { st_release_gpu(&colstep[p], t + 1); st_release_gpu(&colstep[q], t + 1); }
             }

@@ -317,7 +317,12 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
 //   narrow bin (b-a <= 0.2): Taylor/Hermite series about the bin midpoint (erfc differences would cancel)
 //   else   erfc(a) - erfc(b) with a hand-fitted erfcx (1 MUFU.RCP + 1 MUFU.EX2 each), mirrored onto y >= 0
 // ---------------------------------------------------------------------------------------------------------
+#ifndef SQ_R
 #define SQ_R 8
+#endif
+#ifndef SQ_MINB
+#define SQ_MINB 2
+#endif
 #define SQ_TILE (SC_THREADS * SQ_R)
 #define LN2F 0.6931471806f
 #define KINVF 0.8325546112f           // 1/sqrt(log2 e)
@@ -342,7 +347,7 @@ __device__ __forceinline__ float erfc_pos_scaled(float xs) {
     return (p * t) * kb_ex2(-xs * xs);
 }
 
-__global__ void __launch_bounds__(SC_THREADS, 2)
+__global__ void __launch_bounds__(SC_THREADS, SQ_MINB)
 tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
                        const float4 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                        KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
@@ -408,17 +413,26 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
                 const float wj = fabsf(B.z);
                 if (B.z < 0.f && fast_ok) {
                     const float2 w2 = make_float2(wj, wj);
+                    // Horner steps run across the four candidate pairs in lockstep: consecutive FFMA2s then share the
+                    // coefficient operand (operand-reuse cache) and read two fresh register pairs each
+                    float2 tau[SQ_R / 2], z[SQ_R / 2], pp[SQ_R / 2];
 #pragma unroll
                     for (int p = 0; p < SQ_R / 2; p++) {
                         const float2 m = __ffma2_rn(__fadd2_rn(__fadd2_rn(xm[p], nmu), xl[p]), rs, ms);
                         const float2 y = make_float2(fabsf(m.x), fabsf(m.y));
-                        float2 tau = __ffma2_rn(y, qts, make_float2(-1.f, -1.f));
-                        tau = make_float2(fminf(tau.x, 1.f), fminf(tau.y, 1.f));
-                        const float2 z = __fadd2_rn(y, qnh0);
-                        float2 pp = qc[KB_QF_DEG];
+                        const float2 t0 = __ffma2_rn(y, qts, make_float2(-1.f, -1.f));
+                        tau[p] = make_float2(fminf(t0.x, 1.f), fminf(t0.y, 1.f));
+                        z[p] = __fadd2_rn(y, qnh0);
+                        pp[p] = __ffma2_rn(qc[KB_QF_DEG], tau[p], qc[KB_QF_DEG - 1]);
+                    }
 #pragma unroll
-                        for (int i = KB_QF_DEG - 1; i >= 0; i--) pp = __ffma2_rn(pp, tau, qc[i]);
-                        const float2 e = __ffma2_rn(make_float2(-z.x, -z.y), z, pp);
+                    for (int i = KB_QF_DEG - 2; i >= 0; i--) {
+#pragma unroll
+                        for (int p = 0; p < SQ_R / 2; p++) pp[p] = __ffma2_rn(pp[p], tau[p], qc[i]);
+                    }
+#pragma unroll
+                    for (int p = 0; p < SQ_R / 2; p++) {
+                        const float2 e = __ffma2_rn(make_float2(-z[p].x, -z[p].y), z[p], pp[p]);
                         a32[p] = __ffma2_rn(w2, make_float2(kb_ex2(e.x), kb_ex2(e.y)), a32[p]);
                     }
                 } else if (A.z * qn < QUANT_WIDE_THR) {
