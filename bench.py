@@ -353,11 +353,13 @@ def main():
         if k == 1 and ms_k > 0:
             a = ce_cont / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
-                       frac=a / peaks["mufu_ex2_gops"])
+                       frac=a / peaks["mufu_ex2_gops"], traffic=182.6e6,
+                       traffic_note="dram read+write bytes per launch (2^20-candidate chunk), ncu --set full, profiles/r01_ncu_tpe_score.md")
         if k == 2 and ms_k > 0:
             a = ce_quant / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G CDF-pair evals/s (2 exp = 2 MUFU.EX2 each, algorithmic)", achieved=a,
-                       peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2))
+                       peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2), traffic=198.6e6,
+                       traffic_note="dram read+write bytes per launch (2^20-candidate chunk), ncu --set full, profiles/r01_ncu_tpe_score.md")
         if k == 0 and ms_k > 0:
             bytes_alg = float(n_local) * D * 8 * args.steps + float(n_local) * (n_cont * 8 + n_quant * 16) * args.steps
             a = bytes_alg / (ms_k * 1e-3) / 1e9
@@ -367,7 +369,7 @@ def main():
         kern.append(ent)
     dom = max((e for e in kern if "frac" in e), key=lambda e: e["ms_total"])
     roofline = {"bound": dom["bound"], "achieved": dom["achieved"], "peak": dom["peak"], "unit": dom["unit"],
-                "frac": dom["frac"], "traffic": None, "kernel": dom["name"],
+                "frac": dom["frac"], "traffic": dom.get("traffic"), "kernel": dom["name"],
                 "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel on this GPU in this run (of measured); "
                                "MEASURED_PEAKS.json has HBM and bf16 only",
                 "kernels": kern, "measured_peaks": peaks}
