@@ -100,7 +100,7 @@ split_kernel(const double *__restrict__ loss, int n, int npad, double *keys, uin
 // ---- Parzen estimator of one (numeric parameter, side) ---------------------------------------------------
 __global__ void __launch_bounds__(BUILD_THREADS)
 parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ values, int n, int D, int nb,
-              const int32_t *__restrict__ pos, int npad, double *keys_all, uint32_t *idx_all) {
+              const int32_t *__restrict__ pos, int npad_stride, double *keys_all, uint32_t *idx_all) {
     __shared__ double s_red[BUILD_THREADS];
     __shared__ double s_scalar[2];
     __shared__ int s_int[BUILD_THREADS];
@@ -109,8 +109,10 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     KbDim &dm = dims[d];
     const int m = side == 0 ? nb : n - nb;  // observations on this side
     const int K = m + 1;
-    double *keys = keys_all + ((size_t)slot * 2 + side) * npad;
-    uint32_t *idx = idx_all + ((size_t)slot * 2 + side) * npad;
+    double *keys = keys_all + ((size_t)slot * 2 + side) * npad_stride;
+    uint32_t *idx = idx_all + ((size_t)slot * 2 + side) * npad_stride;
+    int npad = 2;  // this side's own power of two (>= K): the below side holds at most 26 entries
+    while (npad < K) npad <<= 1;
     const double low = dm.lo, high = dm.hi, shift = dm.shift;
     double *mu = dm.mu[side], *sg = dm.sigma[side], *w = dm.w[side], *logc = dm.logc[side];
     const int tid = threadIdx.x, nt = blockDim.x;
@@ -297,28 +299,42 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
 }
 
 // ---- categorical parameters: weighted bincount (trial order) + prior weight, log ratio, ranks ------------
+#define CAT_CHUNK 4096
 __global__ void categorical_kernel(KbDim *dims, const int *cat_dims, const double *__restrict__ values, int n, int D,
                                    int nb, const int32_t *__restrict__ pos) {
     __shared__ double s_sum[2];
+    __shared__ int s_pos[CAT_CHUNK];
+    __shared__ unsigned short s_cat[CAT_CHUNK];
     const int d = cat_dims[blockIdx.x];
     KbDim &dm = dims[d];
     const int C = dm.n_choices;
     for (int side = 0; side < 2; side++) {
         const int m = side == 0 ? nb : n - nb;
         double *p = dm.cat_p[side];
-        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        // every thread owns the categories c, c + blockDim, ...: their sums run over the trials IN ORDER (the
+        // oracle's rounding); trials are staged through shared memory a chunk at a time so the scan is on-chip
+        for (int c0 = 0; c0 < C; c0 += blockDim.x) {
+            const int c = c0 + threadIdx.x;
             double acc = 0.0;
-            for (int i = 0; i < n; i++) {
-                int ps = pos[side * n + i];
-                if (ps >= 0 && (int)values[(size_t)i * D + d] == c) acc += tpe_ramp(ps, m);
+            for (int base = 0; base < n; base += CAT_CHUNK) {
+                const int cnt = min(CAT_CHUNK, n - base);
+                __syncthreads();
+                for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+                    s_pos[i] = pos[side * n + base + i];
+                    s_cat[i] = (unsigned short)(int)values[(size_t)(base + i) * D + d];
+                }
+                __syncthreads();
+                if (c < C)
+                    for (int i = 0; i < cnt; i++)
+                        if (s_pos[i] >= 0 && (int)s_cat[i] == c) acc += tpe_ramp(s_pos[i], m);
             }
-            p[c] = acc + 1.0;  // prior_weight
+            if (c < C) p[c] = acc + 1.0;  // prior_weight
         }
         __syncthreads();
         if (threadIdx.x == 0) {
-            double s = 0.0;
-            for (int c = 0; c < C; c++) s += p[c];
-            s_sum[side] = s;
+            double sm = 0.0;
+            for (int c = 0; c < C; c++) sm += p[c];
+            s_sum[side] = sm;
         }
         __syncthreads();
         for (int c = threadIdx.x; c < C; c += blockDim.x) p[c] = p[c] / s_sum[side];
@@ -420,22 +436,27 @@ extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *v
         // numeric dims in slot order = cont and quant lists merged by numeric_slot
         std::vector<int> numeric((size_t)ctx->n_numeric);
         for (int d = 0; d < D; d++) if (ctx->h_dims[(size_t)d].numeric_slot >= 0) numeric[(size_t)ctx->h_dims[(size_t)d].numeric_slot] = d;
-        int *d_numeric = nullptr;
-        KB_CUDA(ctx, cudaMallocAsync(&d_numeric, sizeof(int) * numeric.size(), s));
-        KB_CUDA(ctx, cudaMemcpyAsync(d_numeric, numeric.data(), sizeof(int) * numeric.size(), cudaMemcpyHostToDevice, s));
+        if (!ctx->d_numeric_dims) {
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_numeric_dims, sizeof(int) * numeric.size()));
+            KB_CUDA(ctx, cudaMemcpy(ctx->d_numeric_dims, numeric.data(), sizeof(int) * numeric.size(), cudaMemcpyHostToDevice));
+        }
         parzen_kernel<<<dim3((unsigned)ctx->n_numeric, 2), BUILD_THREADS, 0, s>>>(
-            ctx->d_dims, d_numeric, ctx->d_values, n, D, nb, ctx->d_pos, npad, ctx->d_sort_keys, ctx->d_sort_idx);
+            ctx->d_dims, ctx->d_numeric_dims, ctx->d_values, n, D, nb, ctx->d_pos, npad, ctx->d_sort_keys, ctx->d_sort_idx);
         KB_LAUNCH_CHECK(ctx);
-        KB_CUDA(ctx, cudaStreamSynchronize(s));  // `numeric` must outlive the async copy
-        cudaFreeAsync(d_numeric, s);
     }
     if (ctx->n_cat > 0) {
         categorical_kernel<<<ctx->n_cat, 128, 0, s>>>(ctx->d_dims, ctx->d_cat_dims, ctx->d_values, n, D, nb, ctx->d_pos);
         KB_LAUNCH_CHECK(ctx);
     }
-    // bring back K / Kpad (the pointers are unchanged) so that launches can be sized on the host
-    KB_CUDA(ctx, cudaMemcpyAsync(ctx->h_dims.data(), ctx->d_dims, sizeof(KbDim) * (size_t)D, cudaMemcpyDeviceToHost, s));
-    KB_CUDA(ctx, cudaStreamSynchronize(s));
+    // K / Kpad are known on the host (n_side + 1); p_accept and L stay on the device (kb_tpe_get_parzen fetches them),
+    // so the call returns without synchronising: the kernels above are simply ordered before any scoring launch
+    for (int d = 0; d < D; d++) {
+        KbDim &k = ctx->h_dims[(size_t)d];
+        for (int side = 0; side < 2; side++) {
+            k.K[side] = k.kind == KB_CATEGORICAL ? k.n_choices : (side == 0 ? nb : n - nb) + 1;
+            k.Kpad[side] = k.kind == KB_CATEGORICAL ? k.n_choices : pad_to(k.K[side], KB_TABLE_PAD);
+        }
+    }
     ctx->n_trials = n;
     ctx->n_below = nb;
     ctx->history_ready = true;
@@ -462,6 +483,10 @@ extern "C" int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, doubl
     if (w) KB_CUDA(ctx, cudaMemcpy(w, k.w[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
     if (mu) KB_CUDA(ctx, cudaMemcpy(mu, k.mu[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
     if (sigma) KB_CUDA(ctx, cudaMemcpy(sigma, k.sigma[side], sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost));
-    if (p_accept) *p_accept = k.p_accept[side];
+    if (p_accept) {
+        KbDim dk;
+        KB_CUDA(ctx, cudaMemcpy(&dk, ctx->d_dims + param, sizeof(KbDim), cudaMemcpyDeviceToHost));
+        *p_accept = dk.p_accept[side];
+    }
     return KB_OK;
 }

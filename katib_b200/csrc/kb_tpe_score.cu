@@ -650,6 +650,7 @@ int kb_tpe_free(kb_ctx *ctx) {
     ctx->d_stage_cont = nullptr; ctx->d_stage_quant = nullptr; ctx->d_scores_chunk = nullptr;
     ctx->d_sel = nullptr; ctx->d_tie = nullptr; ctx->d_win = nullptr; ctx->d_win_all = nullptr;
     ctx->chunk_cap = 0;
+    cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
     cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list); cudaFree(ctx->d_tie_count); cudaFree(ctx->d_slot_of_dim); cudaFree(ctx->d_numeric_dims);
     if (ctx->h_win) cudaFreeHost(ctx->h_win);
     ctx->d_tie_score = nullptr; ctx->d_tie_list = nullptr; ctx->d_tie_count = nullptr; ctx->tie_slots = 0; ctx->d_slot_of_dim = nullptr; ctx->d_numeric_dims = nullptr;
@@ -676,7 +677,7 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
         for (int i = 0; i < ctx->n_cat; i++) slot_of[(size_t)ctx->cat_dims[(size_t)i]] = i;
         for (int d = 0; d < D; d++) if (ctx->h_dims[(size_t)d].numeric_slot >= 0) numeric[(size_t)ctx->h_dims[(size_t)d].numeric_slot] = d;
         KB_CUDA(ctx, cudaMalloc(&sc->d_slot_of_dim, sizeof(int) * (size_t)D));
-        KB_CUDA(ctx, cudaMalloc(&sc->d_numeric_dims, sizeof(int) * slots));
+        if (!sc->d_numeric_dims) KB_CUDA(ctx, cudaMalloc(&sc->d_numeric_dims, sizeof(int) * slots));
         KB_CUDA(ctx, cudaMemcpy(sc->d_slot_of_dim, slot_of.data(), sizeof(int) * (size_t)D, cudaMemcpyHostToDevice));
         KB_CUDA(ctx, cudaMemcpy(sc->d_numeric_dims, numeric.data(), sizeof(int) * slots, cudaMemcpyHostToDevice));
     }
@@ -883,8 +884,12 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
     if (!out_value) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest: out_value is NULL");
     cudaStream_t s = ctx->stream;
     const int64_t n = n_ei_candidates;
-    double *d_cand = nullptr;
-    KB_CUDA(ctx, cudaMalloc(&d_cand, sizeof(double) * (size_t)n * ctx->D));
+    if (n * ctx->D > ctx->suggest_cap) {
+        cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_suggest, sizeof(double) * (size_t)n * ctx->D));
+        ctx->suggest_cap = n * ctx->D;
+    }
+    double *d_cand = ctx->d_suggest;
     int rc = kb_tpe_sample_into(ctx, n, seed, d_cand, s);
     const int64_t rows = n < KB_CHUNK_ROWS ? n : KB_CHUNK_ROWS;
     if (!rc) rc = tpe_ensure_scratch(ctx, rows, n, false, false);
@@ -895,7 +900,5 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
         rc = tpe_launch_chunk(ctx, d_cand + (size_t)off * ctx->D, m, off, off, true, nullptr, s);
     }
     if (!rc) rc = tpe_finish_selection(ctx, 0, nullptr, out_value, nullptr, s);
-    cudaStreamSynchronize(s);
-    cudaFree(d_cand);
     return rc;
 }
