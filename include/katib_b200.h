@@ -208,7 +208,7 @@ int kb_peak_measure(kb_ctx *ctx, int which, double *out);
 /* Per-kernel-class device timing with CUDA events on the launching stream.  kb_profile(ctx, 1) starts
  * (and clears) the counters, kb_profile(ctx, 0) stops; kb_profile_read returns the summed duration and
  * the launch count of one class:  0 tpe_stage  1 tpe_score_cont  2 tpe_score_quant  3 tpe_rescore+pick
- * 4 sobol_fill  5 tpe_build  6 tpe_sample  7 cmaes_ask  8 cmaes_tell  9 eigh  10 collective */
+ * 4 sobol_fill  5 tpe_build  6 tpe_sample  7 cmaes_ask  8 cmaes_tell  9 eigh  10 collective  11 dgemm (DMMA) */
 int kb_profile(kb_ctx *ctx, int enable);
 int kb_profile_read(kb_ctx *ctx, int kernel_class, double *ms_total, int64_t *launches);
 /* number of kernels this library has launched on this ctx since creation */

@@ -102,7 +102,10 @@ int kb_dgemm_nt(kb_ctx *ctx, int M, int N, int K, const double *A, int lda, cons
                 double *C, int ldc, double alpha, double beta, cudaStream_t st) {
     if (M <= 0 || N <= 0) return KB_OK;
     dim3 grid((unsigned)((N + GM_BN - 1) / GM_BN), (unsigned)((M + GM_BM - 1) / GM_BM));
-    dgemm_nt_kernel<<<grid, 128, 0, st>>>(M, N, K, A, lda, s, Bm, ldb, C, ldc, alpha, beta);
+    {
+        KbProf pf(ctx, 11, st);
+        dgemm_nt_kernel<<<grid, 128, 0, st>>>(M, N, K, A, lda, s, Bm, ldb, C, ldc, alpha, beta);
+    }
     KB_LAUNCH_CHECK(ctx);
     return KB_OK;
 }
@@ -306,6 +309,138 @@ jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, 
     }
 }
 
+// ---- block version: a CTA owns 2*JB columns in shared memory for a whole local tournament ------------------------
+// Columns are grouped into blocks of JB; the round-robin runs over BLOCK pairs (nblk - 1 outer steps per sweep
+// instead of n - 1), and inside an outer step the CTA orthogonalises all pairs among its 2*JB columns (2*JB - 1 local
+// steps, JB pairs each, one warp per pair) out of shared memory.  Global traffic and the inter-CTA hand-off (same
+// release/acquire counters, per block) are paid once per outer step, so the serial chain is ~JB times shorter.
+#define JB 4
+#define JB_THREADS (32 * JB)
+
+__global__ void __launch_bounds__(JB_THREADS)
+jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh, int *sweep_rot, double tol) {
+    extern __shared__ __align__(16) double s_cols[];  // [2*JB][n] of G, then [2*JB][n] of V
+    double *sG = s_cols, *sV = s_cols + (size_t)2 * JB * n;
+    const int nblk0 = (n + JB - 1) / JB;
+    const int NB = nblk0 + (nblk0 & 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    cg::grid_group grid = cg::this_grid();
+    int t = 0;
+    for (int sweep = 0; sweep < EG_MAX_SWEEPS; sweep++) {
+        int my_rot = 0;
+        for (int r = 0; r < NB - 1; r++, t++) {
+            for (int i = blockIdx.x; i < NB / 2; i += gridDim.x) {
+                int P, Q;
+                rr_pair(NB, r, i, P, Q);
+                if (tid == 0) {
+                    while (ld_acquire_gpu(&blkstep[P]) < t) {}
+                    while (ld_acquire_gpu(&blkstep[Q]) < t) {}
+                }
+                __syncthreads();
+                // global column of local slot s
+                auto col_of = [&](int s) { return (s < JB ? P * JB + s : Q * JB + (s - JB)); };
+                if ((n & 1) == 0) {
+                    // 16-byte loads, all of a batch in flight before the first shared-memory store (memory-level parallelism)
+                    const int n2 = n >> 1;
+                    for (int s0 = 0; s0 < 2 * JB; s0 += 2) {
+                        for (int k0 = 0; k0 < n2; k0 += JB_THREADS * 4) {
+                            double2 g[2][4], v[2][4];
+#pragma unroll
+                            for (int ss = 0; ss < 2; ss++) {
+                                const int c = col_of(s0 + ss);
+#pragma unroll
+                                for (int e = 0; e < 4; e++) {
+                                    const int k = k0 + tid + e * JB_THREADS;
+                                    const bool ok = c < n && k < n2;
+                                    g[ss][e] = ok ? __ldcg(reinterpret_cast<const double2 *>(Gt + (size_t)c * n) + k) : make_double2(0.0, 0.0);
+                                    v[ss][e] = ok ? __ldcg(reinterpret_cast<const double2 *>(Vt + (size_t)c * n) + k) : make_double2(0.0, 0.0);
+                                }
+                            }
+#pragma unroll
+                            for (int ss = 0; ss < 2; ss++)
+#pragma unroll
+                                for (int e = 0; e < 4; e++) {
+                                    const int k = k0 + tid + e * JB_THREADS;
+                                    if (k < n2) {
+                                        reinterpret_cast<double2 *>(sG + (size_t)(s0 + ss) * n)[k] = g[ss][e];
+                                        reinterpret_cast<double2 *>(sV + (size_t)(s0 + ss) * n)[k] = v[ss][e];
+                                    }
+                                }
+                        }
+                    }
+                } else {
+                    for (int s = 0; s < 2 * JB; s++) {
+                        const int c = col_of(s);
+                        for (int k = tid; k < n; k += JB_THREADS) {
+                            sG[(size_t)s * n + k] = c < n ? __ldcg(Gt + (size_t)c * n + k) : 0.0;
+                            sV[(size_t)s * n + k] = c < n ? __ldcg(Vt + (size_t)c * n + k) : 0.0;
+                        }
+                    }
+                }
+                __syncthreads();
+                bool dirty = false;
+                for (int lr = 0; lr < 2 * JB - 1; lr++) {
+                    int a, b;
+                    rr_pair(2 * JB, lr, warp, a, b);
+                    if (col_of(a) < n && col_of(b) < n) {
+                        double *ga = sG + (size_t)a * n, *gb = sG + (size_t)b * n;
+                        double aa = 0.0, bb = 0.0, cc = 0.0, aa2 = 0.0, bb2 = 0.0, cc2 = 0.0;
+                        int k = lane;
+                        for (; k + 32 < n; k += 64) {  // two independent accumulation chains
+                            const double x = ga[k], y = gb[k], x2 = ga[k + 32], y2 = gb[k + 32];
+                            aa += x * x; bb += y * y; cc += x * y;
+                            aa2 += x2 * x2; bb2 += y2 * y2; cc2 += x2 * y2;
+                        }
+                        for (; k < n; k += 32) { const double x = ga[k], y = gb[k]; aa += x * x; bb += y * y; cc += x * y; }
+                        aa = warp_sum(aa + aa2); bb = warp_sum(bb + bb2); cc = warp_sum(cc + cc2);
+                        if (!(fabs(cc) <= tol * sqrt(aa * bb) || cc == 0.0)) {
+                            const double zeta = (bb - aa) / (2.0 * cc);
+                            const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                            const double cs = rsqrt(1.0 + tt * tt), sn = cs * tt;
+                            double *va = sV + (size_t)a * n, *vb = sV + (size_t)b * n;
+                            for (int k = lane; k < n; k += 32) {
+                                const double x = ga[k], y = gb[k];
+                                ga[k] = cs * x - sn * y; gb[k] = sn * x + cs * y;
+                                const double u = va[k], v = vb[k];
+                                va[k] = cs * u - sn * v; vb[k] = sn * u + cs * v;
+                            }
+                            dirty = true;
+                            if (lane == 0) my_rot++;
+                        }
+                    }
+                    __syncthreads();
+                }
+                // write back only if something in this CTA rotated (a block-uniform vote keeps the barrier legal)
+                const int any = __syncthreads_or(dirty ? 1 : 0);
+                if (any) {
+                    for (int s = 0; s < 2 * JB; s++) {
+                        const int c = col_of(s);
+                        if (c >= n) continue;
+                        if ((n & 1) == 0) {
+                            for (int k = tid; k < (n >> 1); k += JB_THREADS) {
+                                __stcg(reinterpret_cast<double2 *>(Gt + (size_t)c * n) + k, reinterpret_cast<const double2 *>(sG + (size_t)s * n)[k]);
+                                __stcg(reinterpret_cast<double2 *>(Vt + (size_t)c * n) + k, reinterpret_cast<const double2 *>(sV + (size_t)s * n)[k]);
+                            }
+                        } else {
+                            for (int k = tid; k < n; k += JB_THREADS) {
+                                __stcg(Gt + (size_t)c * n + k, sG[(size_t)s * n + k]);
+                                __stcg(Vt + (size_t)c * n + k, sV[(size_t)s * n + k]);
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+                if (tid == 0) { st_release_gpu(&blkstep[P], t + 1); st_release_gpu(&blkstep[Q], t + 1); }
+            }
+        }
+        if (lane == 0 && my_rot) atomicAdd(&sweep_rot[sweep], my_rot);
+        grid.sync();
+        const int rot = __ldcg(&sweep_rot[sweep]);
+        if (blockIdx.x == 0 && tid == 0) sh->sweeps = sweep + 1;
+        if (rot == 0) break;
+    }
+}
+
 // lambda_j = v_j . g_j (keeps the sign for indefinite input), then rank by value, canonical signs, write outputs:
 //   w[rank] = lambda, V[i*n + rank] = +-v_j[i]  (row-major, eigenvector `rank` in column `rank`)
 __global__ void eigh_finish_kernel(int n, const double *__restrict__ Gt, const double *__restrict__ Vt, double shift,
@@ -380,13 +515,26 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
         jacobi_onesided_kernel<false><<<1, EG_THREADS, 0, st>>>(n, Gt, Vt, sh, tol);
         KB_LAUNCH_CHECK(ctx);
     } else {
-        int blocks = pairs, per_sm = 0;
-        KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_flag_kernel, EF_THREADS, 0));
-        const int cap = per_sm * ctx->prop.multiProcessorCount;
-        if (blocks > cap) blocks = cap;
         double tolv = tol;
-        void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv};
-        KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_flag_kernel, dim3((unsigned)blocks), dim3(EF_THREADS), args, 0, st));
+        const size_t smem = sizeof(double) * (size_t)4 * JB * n;  // 2*JB columns of G and of V
+        if (smem <= (size_t)ctx->prop.sharedMemPerBlockOptin) {
+            // block version: the 2*JB columns of a block pair live in shared memory for a whole local tournament
+            const int nblk0 = (n + JB - 1) / JB, NB = nblk0 + (nblk0 & 1);
+            KB_CUDA(ctx, cudaFuncSetAttribute(jacobi_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            int blocks = NB / 2, per_sm = 0;
+            KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_block_kernel, JB_THREADS, smem));
+            const int cap = per_sm * ctx->prop.multiProcessorCount;
+            if (blocks > cap) blocks = cap;
+            void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv};
+            KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_block_kernel, dim3((unsigned)blocks), dim3(JB_THREADS), args, smem, st));
+        } else {
+            int blocks = pairs, per_sm = 0;
+            KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_flag_kernel, EF_THREADS, 0));
+            const int cap = per_sm * ctx->prop.multiProcessorCount;
+            if (blocks > cap) blocks = cap;
+            void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv};
+            KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_flag_kernel, dim3((unsigned)blocks), dim3(EF_THREADS), args, 0, st));
+        }
         ctx->launches++;
     }
     eigh_finish_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(n, Gt, Vt, shift, lam, d_w, d_V);
