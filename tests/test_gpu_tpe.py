@@ -203,3 +203,61 @@ def test_config5_shape_reduced(ctx):
     assert errs.max() < TOL, errs
     idx, val, sc = ctx.tpe_score_select(cand)
     assert list(idx) == best
+
+
+def test_multi_chunk_host_path_and_offsets(ctx):
+    """2.5 Mi candidates cross the 2^20-row chunk boundary (double-buffered H2D): winners and indices vs the oracle."""
+    rng = np.random.Generator(np.random.PCG64(8))
+    ctx.space_set([kb.KB_UNIFORM, kb.KB_INT, kb.KB_CATEGORICAL], [0.0, 0, 0], [1.0, 9, 0], None, [0, 0, 4])
+    n = 60
+    vals = np.stack([rng.uniform(0, 1, n), np.floor(rng.uniform(0, 10, n)), np.floor(rng.uniform(0, 4, n))], axis=1)
+    loss = (vals[:, 0] - 0.7) ** 2 + 0.01 * vals[:, 1] + 0.1 * (vals[:, 2] != 2) + rng.normal(0, 0.05, n)
+    ctx.tpe_set_history(vals, loss)
+    nc = (5 << 19) + 12345
+    cand = np.stack([rng.uniform(0, 1, nc), np.floor(rng.uniform(0, 10, nc)), np.floor(rng.uniform(0, 4, nc))], axis=1)
+    idx, val, sc = ctx.tpe_score_select(cand, index_offset=7_000_000_000)
+    _, b0 = O.tpe_score_numeric(cand[:, 0], vals[:, 0], loss, 0.0, 1.0)
+    _, b1 = O.tpe_score_numeric(cand[:, 1], vals[:, 1], loss, -0.5, 9.5, 1.0)
+    _, b2 = O.tpe_score_categorical(cand[:, 2], vals[:, 2], loss, 4)
+    assert list(idx - 7_000_000_000) == [b0, b1, b2]
+    assert list(val) == [cand[b0, 0], cand[b1, 1], cand[b2, 2]]
+
+
+def test_edges_empty_history_empty_candidates_wide_space(ctx):
+    # no history at all: both estimators are the prior alone -> every score is 0 -> first candidate wins
+    ctx.space_set([kb.KB_UNIFORM, kb.KB_CATEGORICAL], [0.0, 0], [1.0, 0], None, [0, 3])
+    ctx.tpe_set_history(np.zeros((0, 2)), np.zeros(0))
+    cand = np.array([[0.3, 2.0], [0.9, 0.0], [0.1, 1.0]])
+    sc = ctx.tpe_scores(cand)
+    assert np.allclose(sc, 0.0, atol=1e-6)
+    assert list(ctx.tpe_score_select(cand)[0]) == [0, 0]
+    idx, val, _ = ctx.tpe_score_select(np.zeros((0, 2)))
+    assert list(idx) == [-1, -1]
+    # 300 parameters, 4096-way categorical, long history (tables stream through several shared-memory stages)
+    rng = np.random.Generator(np.random.PCG64(77))
+    D = 300
+    kinds = [kb.KB_UNIFORM] * 298 + [kb.KB_CATEGORICAL, kb.KB_STEP_INT]
+    lows = [-1.0] * 298 + [0.0, -50.0]
+    highs = [2.0] * 298 + [0.0, 50.0]
+    steps = [0.0] * 298 + [0.0, 5.0]
+    nch = [0] * 298 + [4096, 0]
+    ctx.space_set(kinds, lows, highs, steps, nch)
+    n = 5000
+    vals = rng.uniform(-1, 2, (n, D))
+    vals[:, 298] = np.floor(rng.uniform(0, 4096, n))
+    vals[:, 299] = -50 + 5 * np.floor(rng.uniform(0, 21, n))
+    loss = np.sum(vals[:, :5] ** 2, axis=1) + rng.normal(0, 0.1, n)
+    ctx.tpe_set_history(vals, loss)
+    nc = 700
+    cand = rng.uniform(-1, 2, (nc, D))
+    cand[:, 298] = np.floor(rng.uniform(0, 4096, nc))
+    cand[:, 299] = -50 + 5 * np.floor(rng.uniform(0, 21, nc))
+    got = ctx.tpe_scores(cand)
+    idx = ctx.tpe_score_select(cand)[0]
+    for d in (0, 150, 297):
+        ref, b = O.tpe_score_numeric(cand[:, d], vals[:, d], loss, -1.0, 2.0)
+        assert rel_err(got[:, d], ref) < TOL and idx[d] == b
+    ref, b = O.tpe_score_categorical(cand[:, 298], vals[:, 298], loss, 4096)
+    assert rel_err(got[:, 298], ref) < 1e-12 and idx[298] == b
+    ref, b = O.tpe_score_numeric(cand[:, 299], vals[:, 299], loss, -52.5, 52.5, 5.0)
+    assert rel_err(got[:, 299], ref) < TOL and idx[299] == b
