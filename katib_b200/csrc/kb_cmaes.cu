@@ -262,7 +262,9 @@ static int cma_ensure_eig(kb_ctx *ctx, KbCma *c, cudaStream_t s) {
     if (c->have_eig) return KB_OK;
     const int n = c->n;
     // warm start from the previous generation's eigenvectors (d_Bt holds B^T once a factorisation exists)
-    int rc = kb_eigh_device(ctx, n, c->d_C, 0.0, c->d_lam, c->d_B, c->d_eigws, s, c->have_bt ? c->d_Bt : nullptr, &c->last_sweeps);
+    // no warm start: the Cholesky-preconditioned path (kb_linalg.cu) needs fewer sweeps than a warm start from B_prev,
+    // whose benefit vanishes while the eigenvalues are still clustered (early generations)
+    int rc = kb_eigh_device(ctx, n, c->d_C, 0.0, c->d_lam, c->d_B, c->d_eigws, s, nullptr, &c->last_sweeps);
     if (rc) return rc;
     if ((rc = kb_transpose(ctx, n, n, c->d_B, c->d_Bt, s))) return rc;
     c->have_bt = true;

@@ -13,6 +13,8 @@
 #include <cooperative_groups.h>
 #include <math.h>
 
+#include <algorithm>
+
 #include "kb_internal.cuh"
 #include "kb_linalg.cuh"
 
@@ -318,7 +320,7 @@ jacobi_flag_kernel(int n, double *Gt, double *Vt, int *colstep, EighShared *sh, 
 #define JB_THREADS (32 * JB)
 
 __global__ void __launch_bounds__(JB_THREADS)
-jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh, int *sweep_rot, double tol) {
+jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh, int *sweep_rot, double tol, int with_v) {
     extern __shared__ __align__(16) double s_cols[];  // [2*JB][n] of G, then [2*JB][n] of V
     double *sG = s_cols, *sV = s_cols + (size_t)2 * JB * n;
     const int nblk0 = (n + JB - 1) / JB;
@@ -353,7 +355,7 @@ jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh,
                                     const int k = k0 + tid + e * JB_THREADS;
                                     const bool ok = c < n && k < n2;
                                     g[ss][e] = ok ? __ldcg(reinterpret_cast<const double2 *>(Gt + (size_t)c * n) + k) : make_double2(0.0, 0.0);
-                                    v[ss][e] = ok ? __ldcg(reinterpret_cast<const double2 *>(Vt + (size_t)c * n) + k) : make_double2(0.0, 0.0);
+                                    v[ss][e] = ok && with_v ? __ldcg(reinterpret_cast<const double2 *>(Vt + (size_t)c * n) + k) : make_double2(0.0, 0.0);
                                 }
                             }
 #pragma unroll
@@ -363,7 +365,7 @@ jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh,
                                     const int k = k0 + tid + e * JB_THREADS;
                                     if (k < n2) {
                                         reinterpret_cast<double2 *>(sG + (size_t)(s0 + ss) * n)[k] = g[ss][e];
-                                        reinterpret_cast<double2 *>(sV + (size_t)(s0 + ss) * n)[k] = v[ss][e];
+                                        if (with_v) reinterpret_cast<double2 *>(sV + (size_t)(s0 + ss) * n)[k] = v[ss][e];
                                     }
                                 }
                         }
@@ -373,7 +375,7 @@ jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh,
                         const int c = col_of(s);
                         for (int k = tid; k < n; k += JB_THREADS) {
                             sG[(size_t)s * n + k] = c < n ? __ldcg(Gt + (size_t)c * n + k) : 0.0;
-                            sV[(size_t)s * n + k] = c < n ? __ldcg(Vt + (size_t)c * n + k) : 0.0;
+                            if (with_v) sV[(size_t)s * n + k] = c < n ? __ldcg(Vt + (size_t)c * n + k) : 0.0;
                         }
                     }
                 }
@@ -398,11 +400,18 @@ jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh,
                             const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
                             const double cs = rsqrt(1.0 + tt * tt), sn = cs * tt;
                             double *va = sV + (size_t)a * n, *vb = sV + (size_t)b * n;
-                            for (int k = lane; k < n; k += 32) {
-                                const double x = ga[k], y = gb[k];
-                                ga[k] = cs * x - sn * y; gb[k] = sn * x + cs * y;
-                                const double u = va[k], v = vb[k];
-                                va[k] = cs * u - sn * v; vb[k] = sn * u + cs * v;
+                            if (with_v) {
+                                for (int k = lane; k < n; k += 32) {
+                                    const double x = ga[k], y = gb[k];
+                                    ga[k] = cs * x - sn * y; gb[k] = sn * x + cs * y;
+                                    const double u = va[k], v = vb[k];
+                                    va[k] = cs * u - sn * v; vb[k] = sn * u + cs * v;
+                                }
+                            } else {
+                                for (int k = lane; k < n; k += 32) {
+                                    const double x = ga[k], y = gb[k];
+                                    ga[k] = cs * x - sn * y; gb[k] = sn * x + cs * y;
+                                }
                             }
                             dirty = true;
                             if (lane == 0) my_rot++;
@@ -419,12 +428,12 @@ jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh,
                         if ((n & 1) == 0) {
                             for (int k = tid; k < (n >> 1); k += JB_THREADS) {
                                 __stcg(reinterpret_cast<double2 *>(Gt + (size_t)c * n) + k, reinterpret_cast<const double2 *>(sG + (size_t)s * n)[k]);
-                                __stcg(reinterpret_cast<double2 *>(Vt + (size_t)c * n) + k, reinterpret_cast<const double2 *>(sV + (size_t)s * n)[k]);
+                                if (with_v) __stcg(reinterpret_cast<double2 *>(Vt + (size_t)c * n) + k, reinterpret_cast<const double2 *>(sV + (size_t)s * n)[k]);
                             }
                         } else {
                             for (int k = tid; k < n; k += JB_THREADS) {
                                 __stcg(Gt + (size_t)c * n + k, sG[(size_t)s * n + k]);
-                                __stcg(Vt + (size_t)c * n + k, sV[(size_t)s * n + k]);
+                                if (with_v) __stcg(Vt + (size_t)c * n + k, sV[(size_t)s * n + k]);
                             }
                         }
                     }
@@ -439,6 +448,58 @@ jacobi_block_kernel(int n, double *Gt, double *Vt, int *blkstep, EighShared *sh,
         if (blockIdx.x == 0 && tid == 0) sh->sweeps = sweep + 1;
         if (rot == 0) break;
     }
+}
+
+// ---- Cholesky preconditioning (Demmel-Veselic / Drmac): for a positive definite A = L L^T, one-sided Jacobi on the
+// columns of L converges in far fewer sweeps than on A itself, needs no accumulated V (the eigenvectors are the
+// normalised columns of the converged G, the eigenvalues their squared norms) and resolves small eigenvalues to
+// high relative accuracy.  Right-looking blocked factorisation: a single-CTA panel kernel (panel resident in shared
+// memory) followed by a DMMA rank-pw update of the trailing matrix.  Storage is the column-contiguous Gt.
+#define CH_THREADS 1024
+__global__ void __launch_bounds__(CH_THREADS)
+chol_panel_kernel(int n, int j0, int pw, double *Gt, double *Pt, int *fail) {
+    extern __shared__ __align__(16) double sP[];  // [pw][m], m = n - j0
+    const int m = n - j0, tid = threadIdx.x;
+    if (*fail) return;
+    for (int c = 0; c < pw; c++)
+        for (int i = tid; i < m; i += CH_THREADS) sP[(size_t)c * m + i] = Gt[(size_t)(j0 + c) * n + j0 + i];
+    __syncthreads();
+    for (int c = 0; c < pw; c++) {
+        const double pivot = sP[(size_t)c * m + c];
+        if (!(pivot > 0.0)) {  // not positive definite (or NaN): every thread sees the same value
+            if (tid == 0) *fail = 1;
+            return;
+        }
+        __syncthreads();
+        const double d = sqrt(pivot), inv = 1.0 / d;
+        for (int i = c + tid; i < m; i += CH_THREADS) sP[(size_t)c * m + i] = i == c ? d : sP[(size_t)c * m + i] * inv;
+        __syncthreads();
+        const int rest = pw - c - 1;
+        for (int e = tid; e < rest * m; e += CH_THREADS) {
+            const int c2 = c + 1 + e / m, i = e % m;
+            if (i >= c2) sP[(size_t)c2 * m + i] -= sP[(size_t)c * m + i] * sP[(size_t)c * m + c2];
+        }
+        __syncthreads();
+    }
+    for (int c = 0; c < pw; c++) {
+        for (int i = tid; i < m; i += CH_THREADS) {
+            const double v = i >= c ? sP[(size_t)c * m + i] : 0.0;
+            Gt[(size_t)(j0 + c) * n + j0 + i] = v;
+            if (i >= pw) Pt[(size_t)(i - pw) * pw + c] = v;
+        }
+        for (int i = tid; i < j0; i += CH_THREADS) Gt[(size_t)(j0 + c) * n + i] = 0.0;  // strictly upper part of L
+    }
+}
+// G = V sqrt(Lambda) after Jacobi on L: lambda_j = |g_j|^2 - shift, v_j = g_j / |g_j|
+__global__ void eigh_finish_chol_kernel(int n, const double *__restrict__ Gt, double *Vt, double shift, double *lam) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n) return;
+    double acc = 0.0;
+    for (int k = lane; k < n; k += 32) { const double g = Gt[(size_t)warp * n + k]; acc += g * g; }
+    acc = warp_sum(acc);
+    const double inv = acc > 0.0 ? rsqrt(acc) : 0.0;
+    for (int k = lane; k < n; k += 32) Vt[(size_t)warp * n + k] = Gt[(size_t)warp * n + k] * inv;
+    if (lane == 0) lam[warp] = acc - shift;
 }
 
 // lambda_j = v_j . g_j (keeps the sign for indefinite input), then rank by value, canonical signs, write outputs:
@@ -488,7 +549,7 @@ __global__ void eigh_init_kernel(int n, const double *__restrict__ A, double shi
 
 // workspace: Gt, Vt (n*n each), lam (n), EighShared, per-column step counters, per-sweep rotation counts
 size_t kb_eigh_workspace_bytes(int n) {
-    return sizeof(double) * ((size_t)2 * n * n + n + 2) + sizeof(int) * ((size_t)n + 4 + EG_MAX_SWEEPS) + 256;
+    return sizeof(double) * ((size_t)2 * n * n + n + 2 + (size_t)32 * n) + sizeof(int) * ((size_t)n + 8 + EG_MAX_SWEEPS) + 256;
 }
 
 // d_V0t (optional): transposed eigenvectors of a nearby matrix (row j = vector j).  The iteration then starts from
@@ -498,7 +559,8 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
                    cudaStream_t st, const double *d_V0t, int *sweeps_out) {
     double *Gt = (double *)workspace, *Vt = Gt + (size_t)n * n, *lam = Vt + (size_t)n * n;
     EighShared *sh = (EighShared *)(lam + n + (n & 1));
-    int *colstep = (int *)(sh + 1), *sweep_rot = colstep + n + 2 + (n & 1);
+    int *colstep = (int *)(sh + 1), *sweep_rot = colstep + n + 2 + (n & 1), *chol_fail = sweep_rot + EG_MAX_SWEEPS;
+    double *Pt = (double *)(chol_fail + 4);  // [n][32] panel copy for the trailing update (8-byte aligned: counts above are even)
     KbProf pf(ctx, 9, st);
     const int warm = d_V0t != nullptr && shift == 0.0;
     eigh_init_kernel<<<(unsigned)(((size_t)n * n + 255) / 256), 256, 0, st>>>(n, d_A, shift, Gt, Vt, sh, colstep, sweep_rot, warm);
@@ -511,6 +573,7 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
     const double tol = sqrt((double)n) * 2.220446049250313e-16;  // LAPACK dgesvj-style stopping criterion
     const int pairs = (n + 1) / 2;
     const int warps_per_block = EG_THREADS / 32;
+    bool chol_path = false;
     if (pairs <= warps_per_block * 2) {
         jacobi_onesided_kernel<false><<<1, EG_THREADS, 0, st>>>(n, Gt, Vt, sh, tol);
         KB_LAUNCH_CHECK(ctx);
@@ -520,12 +583,40 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
         if (smem <= (size_t)ctx->prop.sharedMemPerBlockOptin) {
             // block version: the 2*JB columns of a block pair live in shared memory for a whole local tournament
             const int nblk0 = (n + JB - 1) / JB, NB = nblk0 + (nblk0 & 1);
+            int with_v = 1;
+            // Cholesky preconditioning when the panel fits in shared memory and no warm start was asked for
+            int pw = (int)std::min<size_t>(32, (size_t)ctx->prop.sharedMemPerBlockOptin / (sizeof(double) * (size_t)n));
+            if (!warm && pw >= 4) {
+                KB_CUDA(ctx, cudaMemsetAsync(chol_fail, 0, sizeof(int), st));
+                KB_CUDA(ctx, cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  (int)(sizeof(double) * (size_t)pw * n)));
+                for (int j0 = 0; j0 < n; j0 += pw) {
+                    const int w = std::min(pw, n - j0), m = n - j0;
+                    chol_panel_kernel<<<1, CH_THREADS, sizeof(double) * (size_t)w * m, st>>>(n, j0, w, Gt, Pt, chol_fail);
+                    KB_LAUNCH_CHECK(ctx);
+                    if (m > w) {
+                        double *T22 = Gt + (size_t)(j0 + w) * n + (j0 + w);
+                        int rc = kb_dgemm_nt(ctx, m - w, m - w, w, Pt, w, nullptr, Pt, w, T22, n, -1.0, 1.0, st);
+                        if (rc) return rc;
+                    }
+                }
+                int failed = 0;
+                KB_CUDA(ctx, cudaMemcpyAsync(&failed, chol_fail, sizeof(int), cudaMemcpyDeviceToHost, st));
+                KB_CUDA(ctx, cudaStreamSynchronize(st));
+                if (failed) {  // not numerically positive definite: start over on A itself with accumulated V
+                    eigh_init_kernel<<<(unsigned)(((size_t)n * n + 255) / 256), 256, 0, st>>>(n, d_A, shift, Gt, Vt, sh, colstep, sweep_rot, 0);
+                    KB_LAUNCH_CHECK(ctx);
+                } else {
+                    with_v = 0;
+                    chol_path = true;
+                }
+            }
             KB_CUDA(ctx, cudaFuncSetAttribute(jacobi_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int blocks = NB / 2, per_sm = 0;
             KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_block_kernel, JB_THREADS, smem));
             const int cap = per_sm * ctx->prop.multiProcessorCount;
             if (blocks > cap) blocks = cap;
-            void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv};
+            void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv, &with_v};
             KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_block_kernel, dim3((unsigned)blocks), dim3(JB_THREADS), args, smem, st));
         } else {
             int blocks = pairs, per_sm = 0;
@@ -537,7 +628,8 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
         }
         ctx->launches++;
     }
-    eigh_finish_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(n, Gt, Vt, shift, lam, d_w, d_V);
+    if (chol_path) eigh_finish_chol_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(n, Gt, Vt, shift, lam);
+    else eigh_finish_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(n, Gt, Vt, shift, lam, d_w, d_V);
     KB_LAUNCH_CHECK(ctx);
     eigh_order_kernel<<<(unsigned)n, 128, 0, st>>>(n, Vt, lam, d_w, d_V);
     KB_LAUNCH_CHECK(ctx);
