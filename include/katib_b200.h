@@ -200,6 +200,9 @@ int kb_service_get_suggestions(kb_service *svc, const void *request, size_t requ
  * Needs no GPU. */
 int kb_service_validate_algorithm_settings(kb_service *svc, const void *request, size_t request_len);
 const char *kb_service_last_message(const kb_service *svc);
+/* Introspection for tests: 0 CMA-ES population size in use, 1 restarts so far (IPOP / BIPOP), 2 internal trials,
+ * 3 generation tag, 4 Complete observations. */
+long long kb_service_stat(kb_service *svc, int which);
 
 /* ---- measurement helpers (used by bench.py and the profiles) ----------------------------------
  * which: 0 = MUFU.EX2 Gop/s, 1 = FP32 FFMA GFMA/s, 2 = FP64 DFMA GFMA/s, 3 = HBM write GB/s,

@@ -87,6 +87,7 @@ def lib():
         "kb_service_get_suggestions": ([vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)], i32),
         "kb_service_validate_algorithm_settings": ([vp, vp, C.c_size_t], i32),
         "kb_service_last_message": ([vp], C.c_char_p),
+        "kb_service_stat": ([vp, i32], C.c_longlong),
         "kb_profile": ([vp, i32], i32),
         "kb_profile_read": ([vp, i32, C.POINTER(dbl), C.POINTER(i64)], i32),
     }
@@ -143,6 +144,9 @@ class Service:
         code = lib().kb_service_get_suggestions(self._h, request_bytes, len(request_bytes), C.byref(reply), C.byref(n))
         data = C.string_at(reply, n.value) if n.value else b""
         return code, data, self.message()
+
+    def stat(self, which):
+        return int(lib().kb_service_stat(self._h, which))
 
     def validate(self, request_bytes):
         """-> (grpc status code, status message); request_bytes None = nil request"""

@@ -267,7 +267,12 @@ struct kb_service {
     // cmaes
     bool cma_ready = false;
     std::vector<int> cma_dims;  // indices into space of the numeric parameters, sorted by name
-    int cma_generation = 0, cma_popsize = 0;
+    int cma_generation = 0, cma_popsize = 0, cma_popsize0 = 0, cma_opt_generation = 0, cma_funhist_term = 0, cma_restarts = 0;
+    int cma_n_large_restarts = 0;
+    bool cma_small_regime = true;
+    long long cma_small_evals = 0, cma_large_evals = 0;
+    double cma_sigma0 = 0;
+    std::vector<double> cma_funhist;
     std::string last_message;
     std::string reply;
 };
@@ -479,27 +484,72 @@ static double from_unit(const Param &p, double u) {
     }
 }
 
+// (re)create the optimiser: cmaes.Sampler's lazy construction, and the restart of the IPOP / BIPOP strategies
+static Status CmaInit(kb_service *s, int popsize, bool random_mean) {
+    const int n = (int)s->cma_dims.size();
+    std::vector<double> mean((size_t)n), lo((size_t)n), hi((size_t)n);
+    double sigma0 = INFINITY;
+    for (int i = 0; i < n; i++) {
+        const Param &p = s->space[(size_t)s->cma_dims[(size_t)i]];
+        lo[(size_t)i] = p.low; hi[(size_t)i] = p.high;
+        mean[(size_t)i] = p.low + (p.high - p.low) / 2.0;
+        if (random_mean) {  // restarts begin from a uniformly drawn point of the box
+            const double u = (double)(mix_seed((uint64_t)s->algo.seed ^ 0xC3A5C85C97CB3127ull, s->draw_counter++) >> 11) * (1.0 / 9007199254740992.0);
+            mean[(size_t)i] = p.low + u * (p.high - p.low);
+        }
+        sigma0 = std::min(sigma0, (p.high - p.low) / 6.0);
+    }
+    if (s->algo.has_sigma) sigma0 = s->algo.sigma;
+    if (kb_cmaes_create(s->ctx, n, mean.data(), sigma0, popsize, lo.data(), hi.data())) return engine_error(s, "kb_cmaes_create");
+    s->cma_popsize = popsize > 0 ? popsize : 4 + (int)std::floor(3.0 * std::log((double)n));
+    s->cma_sigma0 = sigma0;
+    s->cma_opt_generation = 0;
+    s->cma_funhist_term = 10 + (int)std::ceil(30.0 * n / s->cma_popsize);
+    s->cma_funhist.assign((size_t)2 * s->cma_funhist_term, 0.0);
+    s->cma_ready = true;
+    return Status();
+}
+
+// Optimizer.ShouldStop (the `cmaes` library's termination criteria: tolfun over the recent generations, tolx, tolxup,
+// no-effect coordinate / axis, condition number)
+static bool CmaShouldStop(kb_service *s, Status &st) {
+    const int n = (int)s->cma_dims.size();
+    std::vector<double> mean((size_t)n), C((size_t)n * n), pc((size_t)n), B((size_t)n * n), D((size_t)n);
+    double sigma = 0;
+    int gen = 0;
+    if (kb_cmaes_get_state(s->ctx, mean.data(), &sigma, C.data(), nullptr, pc.data(), B.data(), D.data(), &gen)) {
+        st = engine_error(s, "kb_cmaes_get_state");
+        return false;
+    }
+    const double tolx = 1e-12 * s->cma_sigma0, tolxup = 1e4, tolfun = 1e-12, tolcond = 1e14;
+    if (gen > s->cma_funhist_term) {
+        const auto mm = std::minmax_element(s->cma_funhist.begin(), s->cma_funhist.end());
+        if (*mm.second - *mm.first < tolfun) return true;
+    }
+    bool all_small = true;
+    for (int i = 0; i < n; i++) if (!(sigma * C[(size_t)i * n + i] < tolx && sigma * pc[(size_t)i] < tolx)) all_small = false;
+    if (all_small) return true;
+    const double dmax = *std::max_element(D.begin(), D.end()), dmin = *std::min_element(D.begin(), D.end());
+    if (sigma * dmax > tolxup) return true;
+    for (int i = 0; i < n; i++) if (mean[(size_t)i] == mean[(size_t)i] + 0.2 * sigma * std::sqrt(C[(size_t)i * n + i])) return true;
+    const int ax = gen % n;
+    bool axis_dead = true;
+    for (int i = 0; i < n; i++) if (mean[(size_t)i] != mean[(size_t)i] + 0.1 * sigma * D[(size_t)ax] * B[(size_t)i * n + ax]) axis_dead = false;
+    if (axis_dead) return true;
+    return dmax / dmin > tolcond;
+}
+
 static Status CmaStep(kb_service *s, std::vector<double> &x_out) {
     // cmaes.Sampler.SampleRelative: numeric parameters sorted by name; lazily created optimiser; Tell once popsize
-    // Complete trials of the current generation exist; then Ask one solution
+    // Complete trials of the current generation exist; restart check; then Ask one solution
     if (!s->cma_ready) {
         s->cma_dims.clear();
         for (size_t i = 0; i < s->space.size(); i++) if (s->space[i].kind != KB_CATEGORICAL) s->cma_dims.push_back((int)i);
         std::sort(s->cma_dims.begin(), s->cma_dims.end(), [&](int a, int b) { return s->space[(size_t)a].name < s->space[(size_t)b].name; });
-        const int n = (int)s->cma_dims.size();
-        std::vector<double> mean((size_t)n), lo((size_t)n), hi((size_t)n);
-        double sigma0 = INFINITY;
-        for (int i = 0; i < n; i++) {
-            const Param &p = s->space[(size_t)s->cma_dims[(size_t)i]];
-            lo[(size_t)i] = p.low; hi[(size_t)i] = p.high;
-            mean[(size_t)i] = p.low + (p.high - p.low) / 2.0;
-            sigma0 = std::min(sigma0, (p.high - p.low) / 6.0);
-        }
-        if (s->algo.has_sigma) sigma0 = s->algo.sigma;
-        if (kb_cmaes_create(s->ctx, n, mean.data(), sigma0, 0, lo.data(), hi.data())) return engine_error(s, "kb_cmaes_create");
-        s->cma_popsize = 4 + (int)std::floor(3.0 * std::log((double)n));
+        Status st = CmaInit(s, 0, false);
+        if (st.code) return st;
+        s->cma_popsize0 = s->cma_popsize;
         s->cma_generation = 0;
-        s->cma_ready = true;
     }
     const int n = (int)s->cma_dims.size();
     std::vector<const InternalTrial *> sol;
@@ -513,7 +563,39 @@ static Status CmaStep(kb_service *s, std::vector<double> &x_out) {
         }
         if (kb_cmaes_tell(s->ctx, X.data(), f.data())) return engine_error(s, "kb_cmaes_tell");
         for (InternalTrial &t : s->trials) if (t.cma_generation == s->cma_generation) t.cma_told = true;
-        s->cma_generation += 1;
+        s->cma_generation += 1;      // the tag written on trials keeps counting across restarts
+        s->cma_opt_generation += 1;  // the optimiser's own generation restarts with it
+        const auto mm = std::minmax_element(f.begin(), f.end());
+        const size_t slot = (size_t)2 * (size_t)(s->cma_opt_generation % s->cma_funhist_term);
+        s->cma_funhist[slot] = *mm.first; s->cma_funhist[slot + 1] = *mm.second;
+        if (s->algo.restart != "none") {
+            Status st;
+            const bool stop = CmaShouldStop(s, st);
+            if (st.code) return st;
+            if (stop) {
+                int popsize;
+                if (s->algo.restart == "ipop") {
+                    popsize = s->cma_popsize * 2;  // cmaes.SamplerOptionIPop(2), converter.go:60
+                } else {                          // bipop, cmaes.SamplerOptionBIPop(2), converter.go:62
+                    const long long n_eval = (long long)s->cma_popsize * s->cma_opt_generation;
+                    (s->cma_small_regime ? s->cma_small_evals : s->cma_large_evals) += n_eval;
+                    if (s->cma_small_evals < s->cma_large_evals) {
+                        s->cma_small_regime = true;
+                        const double mult = std::pow(2.0, (double)s->cma_n_large_restarts);
+                        const double u = (double)(mix_seed((uint64_t)s->algo.seed ^ 0x9FB21C651E98DF25ull, s->draw_counter++) >> 11) * (1.0 / 9007199254740992.0);
+                        popsize = (int)std::floor(s->cma_popsize0 * std::pow(mult, u * u));
+                    } else {
+                        s->cma_small_regime = false;
+                        s->cma_n_large_restarts += 1;
+                        popsize = s->cma_popsize0 * (1 << std::min(s->cma_n_large_restarts, 20));
+                    }
+                }
+                popsize = std::max(2, std::min(popsize, 1 << 20));
+                Status st2 = CmaInit(s, popsize, true);
+                if (st2.code) return st2;
+                s->cma_restarts += 1;
+            }
+        }
     }
     x_out.assign((size_t)n, 0.0);
     const uint64_t seed = mix_seed((uint64_t)s->algo.seed, s->draw_counter++);
@@ -665,4 +747,18 @@ extern "C" int kb_service_validate_algorithm_settings(kb_service *s, const void 
     }
     s->last_message = st.msg;
     return st.code;
+}
+
+// which: 0 = CMA-ES population size in use, 1 = restarts so far, 2 = internal trials, 3 = generation tag, 4 = Complete observations
+extern "C" long long kb_service_stat(kb_service *s, int which) {
+    if (!s) return -1;
+    std::lock_guard<std::mutex> lk(s->mu);
+    switch (which) {
+        case 0: return s->cma_popsize;
+        case 1: return s->cma_restarts;
+        case 2: return (long long)s->trials.size();
+        case 3: return s->cma_generation;
+        case 4: { long long c = 0; for (const InternalTrial &t : s->trials) c += t.state == ST_COMPLETE; return c; }
+        default: return -1;
+    }
 }

@@ -123,3 +123,28 @@ def test_maximize_direction_is_honoured():
         trials.append(_pb.trial(f"t{r}", a, "SUCCEEDED", [("acc", repr(x))]))  # larger x is better
     assert np.mean(xs[-15:]) > np.mean(xs[:8]) + 0.1
     svc.close()
+
+
+@pytest.mark.parametrize("strategy", ["ipop", "bipop"])
+def test_cmaes_restart_strategies(strategy):
+    """restart_strategy (converter.go:56-65): on a flat objective the tolfun criterion fires once the history of best /
+    worst values spans 10 + ceil(30 n / popsize) generations; IPOP then doubles the population, BIPOP alternates regimes."""
+    svc = kb.Service(0)
+    space = [_pb.parameter("a", "DOUBLE", max="1", min="0"), _pb.parameter("b", "DOUBLE", max="1", min="0")]
+    e = _pb.experiment("r", "cmaes", [("random_state", "3"), ("restart_strategy", strategy)], "MINIMIZE", "loss", space)
+    trials = []
+    pop0 = None
+    for r in range(400):
+        code, reply, msg = svc.get_suggestions(_pb.get_suggestions_request(e, trials, 1, r + 1))
+        assert code == OK, msg
+        a = _pb.parse_reply(reply)[0]
+        assert all(0.0 <= float(v) <= 1.0 for _, v in a)
+        trials.append(_pb.trial(f"t{r}", a, "SUCCEEDED", [("loss", "1.0")]))  # flat objective
+        pop0 = pop0 or svc.stat(0)
+        if svc.stat(1) >= 2:
+            break
+    assert pop0 == 6  # 4 + floor(3 ln 2)
+    assert svc.stat(1) >= 1, "no restart happened"
+    if strategy == "ipop":
+        assert svc.stat(0) == pop0 * 2 ** svc.stat(1)
+    svc.close()
