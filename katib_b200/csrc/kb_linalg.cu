@@ -100,9 +100,144 @@ dgemm_nt_kernel(int M, int N, int K, const double *__restrict__ A, int lda, cons
         }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// the tuned path: CTA tile 128 x 128, 8 warps (2 x 4), warp tile 64 x 32 = 8 x 4 m8n8k4 tiles, BK = 16, three
+// cp.async (LDGSTS, 16 B) stages in dynamic shared memory, rows padded to 20 doubles so that both fragment loads are
+// bank-conflict free, optional split-K (grid.z) with FP64 atomics when the output has too few tiles to fill 148 SMs.
+// Requires even K / lda / ldb and 16-byte aligned operands; anything else takes dgemm_nt_kernel above.
+// ---------------------------------------------------------------------------------------------------------------
+#define GF_BM 128
+#define GF_BN 128
+#define GF_BK 16
+#define GF_LD 20
+#define GF_STAGES 3
+#define GF_THREADS 256
+#define GF_SMEM (GF_STAGES * (GF_BM + GF_BN) * GF_LD * 8 + GF_STAGES * GF_BK * 8)
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem, int src_bytes) {
+    const unsigned int sa = (unsigned int)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(GF_THREADS, 1)
+dgemm_nt_fast_kernel(int M, int N, int K, const double *__restrict__ A, int lda, const double *__restrict__ s,
+                     const double *__restrict__ Bm, int ldb, double *__restrict__ C, int ldc, double alpha, double beta,
+                     int k_per_split) {
+    extern __shared__ __align__(16) double gsm[];
+    double *As = gsm;                                        // [STAGES][BM][LD]
+    double *Bs = gsm + GF_STAGES * GF_BM * GF_LD;            // [STAGES][BN][LD]
+    double *Ss = Bs + GF_STAGES * GF_BN * GF_LD;             // [STAGES][BK] scale slice
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.y * GF_BM, n0 = blockIdx.x * GF_BN;
+    const int kbeg = blockIdx.z * k_per_split, kend = min(K, kbeg + k_per_split);
+    const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    // 128 rows x 8 chunks (16 B = 2 doubles) per operand and stage: 1024 chunks / 256 threads = 4 each
+    auto issue = [&](int stage, int k0) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int chunk = tid + e * GF_THREADS, row = chunk >> 3, kc = (chunk & 7) * 2;
+            const int k = k0 + kc;
+            const int okA = (m0 + row < M && k < kend) ? 16 : 0, okB = (n0 + row < N && k < kend) ? 16 : 0;
+            cp_async16(As + ((size_t)stage * GF_BM + row) * GF_LD + kc, okA ? (const void *)(A + (size_t)(m0 + row) * lda + k) : (const void *)A, okA);
+            cp_async16(Bs + ((size_t)stage * GF_BN + row) * GF_LD + kc, okB ? (const void *)(Bm + (size_t)(n0 + row) * ldb + k) : (const void *)Bm, okB);
+        }
+        if (s && tid < GF_BK / 2) {
+            const int k = k0 + tid * 2;
+            const int ok = k < kend ? 16 : 0;
+            cp_async16(Ss + stage * GF_BK + tid * 2, ok ? (const void *)(s + k) : (const void *)s, ok);
+        }
+    };
+    const int nk = (kend - kbeg + GF_BK - 1) / GF_BK;
+    for (int st = 0; st < GF_STAGES - 1; st++) {
+        if (st < nk) issue(st, kbeg + st * GF_BK);
+        cp_async_commit();
+    }
+    for (int kt = 0; kt < nk; kt++) {
+        cp_async_wait<GF_STAGES - 2>();
+        __syncthreads();
+        if (kt + GF_STAGES - 1 < nk) issue((kt + GF_STAGES - 1) % GF_STAGES, kbeg + (kt + GF_STAGES - 1) * GF_BK);
+        cp_async_commit();
+        const int st = kt % GF_STAGES;
+        const double *as = As + (size_t)st * GF_BM * GF_LD, *bs = Bs + (size_t)st * GF_BN * GF_LD, *ss = Ss + st * GF_BK;
+#pragma unroll
+        for (int kk = 0; kk < GF_BK; kk += 4) {
+            double af[8], bf[4];
+            const double sc = s ? ss[kk + t] : 1.0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) af[i] = as[(wm + i * 8 + g) * GF_LD + kk + t] * sc;
+#pragma unroll
+            for (int j = 0; j < 4; j++) bf[j] = bs[(wn + j * 8 + g) * GF_LD + kk + t];
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) dmma_m8n8k4(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+        }
+    }
+    const bool split = gridDim.z > 1;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int r = m0 + wm + i * 8 + g, c = n0 + wn + j * 8 + 2 * t;
+            if (r < M) {
+#pragma unroll
+                for (int e = 0; e < 2; e++)
+                    if (c + e < N) {
+                        double *p = C + (size_t)r * ldc + c + e;
+                        if (split) atomicAdd(p, alpha * acc[i][j][e]);  // C was zeroed (beta = 0) or kept (beta = 1) by the host
+                        else *p = beta == 0.0 ? alpha * acc[i][j][e] : alpha * acc[i][j][e] + beta * *p;
+                    }
+            }
+        }
+}
+
+__global__ void scale_matrix_kernel(int M, int N, double *C, int ldc, double beta) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)M * N) return;
+    double *p = C + (idx / N) * ldc + idx % N;
+    *p = beta == 0.0 ? 0.0 : *p * beta;
+}
+
 int kb_dgemm_nt(kb_ctx *ctx, int M, int N, int K, const double *A, int lda, const double *s, const double *Bm, int ldb,
                 double *C, int ldc, double alpha, double beta, cudaStream_t st) {
     if (M <= 0 || N <= 0) return KB_OK;
+    const bool aligned = ((K | lda | ldb) & 1) == 0 && (((uintptr_t)A | (uintptr_t)Bm | (uintptr_t)(s ? s : A)) & 15) == 0;
+    if (aligned && K >= 32 && (long long)M * N >= 128 * 128) {
+        static bool attr_done = false;
+        if (!attr_done) {
+            KB_CUDA(ctx, cudaFuncSetAttribute(dgemm_nt_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GF_SMEM));
+            attr_done = true;
+        }
+        const int tiles = ((M + GF_BM - 1) / GF_BM) * ((N + GF_BN - 1) / GF_BN);
+        int splits = 1;
+        const int sms = ctx->prop.multiProcessorCount;
+        if (tiles < sms) {  // too few output tiles: split K so that about one wave of CTAs exists
+            splits = std::min((sms + tiles - 1) / tiles, std::max(1, K / 64));
+            splits = std::min(splits, 32);
+        }
+        int kps = (K + splits - 1) / splits;
+        kps = (kps + GF_BK - 1) / GF_BK * GF_BK;
+        splits = (K + kps - 1) / kps;
+        KbProf pf(ctx, 11, st);
+        if (splits > 1 && beta != 1.0) {
+            scale_matrix_kernel<<<(unsigned)(((size_t)M * N + 255) / 256), 256, 0, st>>>(M, N, C, ldc, beta);
+            ctx->launches++;
+        }
+        dim3 grid((unsigned)((N + GF_BN - 1) / GF_BN), (unsigned)((M + GF_BM - 1) / GF_BM), (unsigned)splits);
+        dgemm_nt_fast_kernel<<<grid, GF_THREADS, GF_SMEM, st>>>(M, N, K, A, lda, s, Bm, ldb, C, ldc, alpha, beta, kps);
+        KB_LAUNCH_CHECK(ctx);
+        return KB_OK;
+    }
     dim3 grid((unsigned)((N + GM_BN - 1) / GM_BN), (unsigned)((M + GM_BM - 1) / GM_BM));
     {
         KbProf pf(ctx, 11, st);
