@@ -87,6 +87,14 @@ int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, const double *l
  * below/above split and both Parzen estimators of every parameter. */
 int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss);
 
+/* Options of the TPE path.  KB_OPT_MERGE_DUPLICATES (default 0): components of an estimator that have identical
+ * (mu, sigma) are folded into one with the summed weight before scoring.  The mixture is the same function (scores
+ * agree to rounding) but has far fewer terms for integer / stepped parameters, whose histories are mostly repeats.
+ * goptuna evaluates every observation separately; the default reproduces that count.  Takes effect at the next
+ * kb_tpe_set_history.  kb_service_* switches it on. */
+#define KB_OPT_MERGE_DUPLICATES 1
+int kb_tpe_set_option(kb_ctx *ctx, int option, int value);
+
 /* Estimator of parameter `param`, side 0 = below (l), 1 = above (g): K entries sorted by mu.
  * Buffers hold `cap` doubles; *K is set even when cap is too small (then KB_ERR_INVALID).
  * For CATEGORICAL parameters mu/sigma are NULL-able and w receives the n_choices probabilities. */

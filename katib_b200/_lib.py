@@ -63,6 +63,7 @@ def lib():
         "kb_comm_world": ([vp, C.POINTER(i32), C.POINTER(i32)], i32),
         "kb_space_set": ([vp, i32, vp, vp, vp, vp, vp], i32),
         "kb_tpe_set_history": ([vp, i64, vp, vp], i32),
+        "kb_tpe_set_option": ([vp, i32, i32], i32),
         "kb_tpe_get_parzen": ([vp, i32, i32, C.POINTER(i32), vp, vp, vp, i32, C.POINTER(dbl)], i32),
         "kb_tpe_scores": ([vp, i64, vp, vp], i32),
         "kb_tpe_score_select": ([vp, i64, vp, i64, vp, vp, vp], i32),
@@ -228,6 +229,9 @@ class Context:
         nch = np.ascontiguousarray(n_choices if n_choices is not None else np.zeros(D), dtype=np.int32)
         self._ck(lib().kb_space_set(self._h, D, _ptr(kind), _ptr(low), _ptr(high), _ptr(step), _ptr(nch)))
         self.D = D
+
+    def tpe_set_option(self, option, value):
+        self._ck(lib().kb_tpe_set_option(self._h, option, value))
 
     def tpe_set_history(self, values, loss):
         values, loss = _f64(values), _f64(loss)

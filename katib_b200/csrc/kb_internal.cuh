@@ -110,6 +110,7 @@ struct kb_ctx {
     double *d_tabmem = nullptr;      // arena behind the KbDim table pointers
     size_t tabmem_bytes = 0;
     bool history_ready = false;
+    bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
 
     // scoring scratch
     int64_t chunk_cap = 0;           // candidates per staged chunk

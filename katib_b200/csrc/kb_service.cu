@@ -674,6 +674,7 @@ static Status InitAtFirstRun(kb_service *s, const ExperimentMsg &e) {
     for (size_t i = 0; i < D; i++) { kind[i] = sp[i].kind; lo[i] = sp[i].low; hi[i] = sp[i].high; st[i] = sp[i].step; nch[i] = (int32_t)sp[i].choices.size(); }
     if (kb_space_set(s->ctx, (int)D, kind.data(), lo.data(), hi.data(), st.data(), nch.data()))
         return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(s->ctx));
+    kb_tpe_set_option(s->ctx, KB_OPT_MERGE_DUPLICATES, 1);  // same mixture, fewer terms (see katib_b200.h)
     s->algo = a; s->space = sp;
     s->maximize = e.objective_type != 1;  // toGoptunaDirection: MINIMIZE -> minimise, anything else -> maximise
     s->initialised = true;

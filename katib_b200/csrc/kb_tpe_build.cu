@@ -100,7 +100,7 @@ split_kernel(const double *__restrict__ loss, int n, int npad, double *keys, uin
 // ---- Parzen estimator of one (numeric parameter, side) ---------------------------------------------------
 __global__ void __launch_bounds__(BUILD_THREADS)
 parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ values, int n, int D, int nb,
-              const int32_t *__restrict__ pos, int npad_stride, double *keys_all, uint32_t *idx_all) {
+              const int32_t *__restrict__ pos, int npad_stride, double *keys_all, uint32_t *idx_all, int merge) {
     __shared__ double s_red[BUILD_THREADS];
     __shared__ double s_scalar[2];
     __shared__ int s_int[BUILD_THREADS];
@@ -108,7 +108,8 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     const int d = numeric_dims[slot];
     KbDim &dm = dims[d];
     const int m = side == 0 ? nb : n - nb;  // observations on this side
-    const int K = m + 1;
+    const int K0 = m + 1;  // components before the optional merge
+    int K = K0;
     double *keys = keys_all + ((size_t)slot * 2 + side) * npad_stride;
     uint32_t *idx = idx_all + ((size_t)slot * 2 + side) * npad_stride;
     int npad = 2;  // this side's own power of two (>= K): the below side holds at most 26 entries
@@ -184,6 +185,43 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
         }
     }
     __syncthreads();
+    // Optional (kb_tpe_set_option KB_OPT_MERGE_DUPLICATES): components with identical (mu, sigma) are one component
+    // with the summed weight -- the same mixture, fewer terms.  Histories of integer / stepped parameters consist
+    // almost entirely of such duplicates (10 000 observations on 64 levels leave ~200 distinct components).  Equal
+    // (mu, sigma) pairs are adjacent after the sort, so this is a run-length compaction; weights add up in order.
+    if (merge && K > 1) {
+        double *tmp_sg = reinterpret_cast<double *>(dm.tab[side]);  // the FP32 table area is not written yet
+        for (int j = tid; j < K; j += nt) idx[j] = (j == 0 || mu[j] != mu[j - 1] || sg[j] != sg[j - 1]) ? 1u : 0u;
+        __syncthreads();
+        const int seg = (K + nt - 1) / nt, b0 = tid * seg, b1 = min(K, b0 + seg);
+        int c = 0;
+        for (int j = b0; j < b1; j++) c += (int)idx[j];
+        s_int[tid] = c;
+        __syncthreads();
+        for (int off = 1; off < nt; off <<= 1) {
+            int v = tid >= off ? s_int[tid - off] : 0;
+            __syncthreads();
+            s_int[tid] += v;
+            __syncthreads();
+        }
+        const int Knew = s_int[nt - 1];
+        int base = s_int[tid] - c;
+        __syncthreads();
+        for (int j = b0; j < b1; j++)
+            if (idx[j]) { idx[j] = 0x80000000u | (uint32_t)base; base++; }
+        __syncthreads();
+        for (int j = tid; j < K; j += nt) {
+            if (!(idx[j] & 0x80000000u)) continue;  // heads only: sum the run in order
+            const int p = (int)(idx[j] & 0x7FFFFFFFu);
+            double ws = w[j];
+            for (int jj = j + 1; jj < K && !(idx[jj] & 0x80000000u); jj++) ws += w[jj];
+            keys[p] = ws; logc[p] = mu[j]; tmp_sg[p] = sg[j];
+        }
+        __syncthreads();
+        for (int p = tid; p < Knew; p += nt) { w[p] = keys[p]; mu[p] = logc[p]; sg[p] = tmp_sg[p]; }
+        __syncthreads();
+        K = Knew;
+    }
     // p_accept = sum_j w_j (Phi(high) - Phi(low)); terms in parallel, summed in order by one thread
     for (int j = tid; j < K; j += nt) {
         double den = sqrt(2.0) * sg[j];
@@ -221,7 +259,7 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     const double LOG2E = 1.4426950408889634;
     float4 *tab = dm.tab[side];
     const bool quant = dm.q > 0.0;
-    double dd2 = 1.0 + (double)K;
+    double dd2 = 1.0 + (double)K0;
     if (dd2 > 100.0) dd2 = 100.0;
     const double minsigma2 = 1.0 * (high - low) / dd2;  // the magic-clip floor (same expression as above)
     if (quant && tid == 0) {
@@ -441,7 +479,8 @@ extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *v
             KB_CUDA(ctx, cudaMemcpy(ctx->d_numeric_dims, numeric.data(), sizeof(int) * numeric.size(), cudaMemcpyHostToDevice));
         }
         parzen_kernel<<<dim3((unsigned)ctx->n_numeric, 2), BUILD_THREADS, 0, s>>>(
-            ctx->d_dims, ctx->d_numeric_dims, ctx->d_values, n, D, nb, ctx->d_pos, npad, ctx->d_sort_keys, ctx->d_sort_idx);
+            ctx->d_dims, ctx->d_numeric_dims, ctx->d_values, n, D, nb, ctx->d_pos, npad, ctx->d_sort_keys, ctx->d_sort_idx,
+            ctx->tpe_merge ? 1 : 0);
         KB_LAUNCH_CHECK(ctx);
     }
     if (ctx->n_cat > 0) {
@@ -471,7 +510,12 @@ extern "C" int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, doubl
     if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_get_parzen: no history set");
     if (param < 0 || param >= ctx->D || (side != 0 && side != 1))
         return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_get_parzen: param/side out of range");
-    const KbDim &k = ctx->h_dims[(size_t)param];
+    KbDim k = ctx->h_dims[(size_t)param];
+    // kb_tpe_set_history returns without waiting; the context's stream is non-blocking, so plain cudaMemcpy does not
+    // order behind the build kernels by itself
+    KB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->tpe_merge && k.kind != KB_CATEGORICAL)  // merged tables: the component count is decided on the device
+        KB_CUDA(ctx, cudaMemcpy(&k, ctx->d_dims + param, sizeof(KbDim), cudaMemcpyDeviceToHost));
     const int n = k.K[side];
     if (K) *K = n;
     if (cap < n) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_get_parzen: cap=%d < K=%d", cap, n);
@@ -489,4 +533,15 @@ extern "C" int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, doubl
         *p_accept = dk.p_accept[side];
     }
     return KB_OK;
+}
+
+extern "C" int kb_tpe_set_option(kb_ctx *ctx, int option, int value) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (option == KB_OPT_MERGE_DUPLICATES) {
+        ctx->tpe_merge = value != 0;
+        ctx->history_ready = false;  // tables must be rebuilt under the new setting
+        return KB_OK;
+    }
+    return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_option: unknown option %d", option);
 }

@@ -1,0 +1,62 @@
+"""KB_OPT_MERGE_DUPLICATES: folding components with identical (mu, sigma) leaves the mixture -- hence every score and
+every winner -- unchanged, while the tables of integer / stepped parameters shrink by an order of magnitude."""
+import numpy as np
+import pytest
+
+import _oracle as O
+import katib_b200 as kb
+from test_gpu_tpe import MIXED, make_history, oracle_scores, rel_err, sample_candidates
+
+pytestmark = pytest.mark.gpu
+KB_OPT_MERGE_DUPLICATES = 1
+
+
+def test_merged_tables_score_like_unmerged_and_like_the_oracle():
+    rng = np.random.Generator(np.random.PCG64(321))
+    sp = MIXED
+    n = 4000
+    vals = make_history(rng, n, sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    loss = (vals[:, 0] - 1.0) ** 2 + 0.05 * (vals[:, 1] - 3) ** 2 + (vals[:, 2] != 1) + rng.normal(0, 0.5, n)
+    cand = sample_candidates(rng, 3000, sp, vals)
+    ref, best = oracle_scores(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"], vals, loss, cand)
+    out = {}
+    for merge in (0, 1):
+        ctx = kb.Context(0)
+        ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+        ctx.tpe_set_option(KB_OPT_MERGE_DUPLICATES, merge)
+        ctx.tpe_set_history(vals, loss)
+        sizes = [len(ctx.tpe_get_parzen(d, 1)[0]) for d in range(len(sp["kinds"]))]
+        out[merge] = (ctx.tpe_scores(cand), ctx.tpe_score_select(cand)[0], sizes)
+        for d, k in enumerate(sp["kinds"]):
+            if k != kb.KB_CATEGORICAL:
+                w = ctx.tpe_get_parzen(d, 1)[0]
+                assert abs(w.sum() - 1.0) < 1e-12
+        ctx.close()
+    s0, i0, k0 = out[0]
+    s1, i1, k1 = out[1]
+    for d, k in enumerate(sp["kinds"]):
+        assert rel_err(s1[:, d], ref[:, d]) < 1e-5 and rel_err(s1[:, d], s0[:, d]) < 5e-6, d
+    assert list(i0) == best and list(i1) == best
+    # INT [-10, 10] (21 levels), DISCRETE 0.25 on [0, 16] (65 levels), STEP_INT 3 on [0, 30] (11 levels): ~3 per level
+    assert k0[1] == n - 25 + 1 and k1[1] <= 3 * 21 + 2
+    assert k1[3] <= 3 * 65 + 2 and k1[4] <= 3 * 11 + 2
+    assert k1[1] >= 21 and k1[3] >= 65 and k1[4] >= 11
+    assert k1[0] == k0[0]  # continuous values are all distinct: nothing to merge
+    print("above-mixture sizes unmerged", k0, "merged", k1)
+
+
+def test_service_uses_merged_tables_transparently():
+    import _pb
+    svc = kb.Service(0)
+    space = [_pb.parameter("layers", "INT", max="5", min="2"), _pb.parameter("lr", "DOUBLE", max="0.03", min="0.01")]
+    e = _pb.experiment("m", "tpe", [("random_state", "1")], "MINIMIZE", "loss", space)
+    trials = []
+    for r in range(40):
+        code, reply, msg = svc.get_suggestions(_pb.get_suggestions_request(e, trials, 1, r + 1))
+        assert code == 0, msg
+        a = _pb.parse_reply(reply)[0]
+        d = dict(a)
+        f = (float(d["lr"]) - 0.02) ** 2 * 1e4 + 0.1 * int(d["layers"])
+        trials.append(_pb.trial(f"t{r}", a, "SUCCEEDED", [("loss", repr(f))]))
+    assert svc.stat(4) == 39
+    svc.close()
