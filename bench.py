@@ -327,6 +327,22 @@ def main():
         else:
             e2e = {"value": None, "unit": "candidates/s", "note": pinned_note}
 
+    # ---- secondary: the same step with KB_OPT_MERGE_DUPLICATES (what kb_service_* runs with).  Reported beside the
+    # headline, never as it: the headline and the roofline count every one of the reference's n+1 components.
+    merged = None
+    if os.environ.get("KB_BENCH_MERGED", "1") == "1":
+        ctx.tpe_set_option(1, 1)
+        ctx.tpe_set_history(vals, loss)
+        k_merged = [len(ctx.tpe_get_parzen(d, 1)[0]) for d in range(D)] if rank == 0 else None
+        for _ in range(min(2, args.warmup)):
+            step_dev()
+        ms_m, wall_m, res_m = timed(step_dev, args.steps)
+        assert np.array_equal(res[0], res_m[0]), "merged-table winners differ from the unmerged run"
+        merged = {"value": n_total * args.steps / (ms_m * 1e-3), "unit": "candidates/s", "ms_per_step": ms_m / args.steps,
+                  "components_above_per_param": k_merged,
+                  "note": "identical mixture and winners; duplicate (mu, sigma) components of int/discrete parameters folded"}
+        ctx.tpe_set_option(1, 0)
+
     def shutdown():
         # orderly exit on every rank: the library's NCCL communicator goes first, on all ranks together, then torch's
         torch.cuda.synchronize()
@@ -384,6 +400,7 @@ def main():
            "cpu_baseline": {"value": cpu_v, "unit": "candidates/s", "cores": cores, "kind": "port",
                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
+           "merged_duplicates": merged,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
     print(json.dumps(out), flush=True)
     shutdown()
