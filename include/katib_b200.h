@@ -86,12 +86,17 @@ int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, const double *l
  * (toGoptunaDirection, converter.go:31-36).  It uploads the history and builds, on the GPU, the
  * below/above split and both Parzen estimators of every parameter. */
 int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss);
+/* Appends n_new trials to the history already on the device and rebuilds the estimators: the same result as
+ * kb_tpe_set_history with the concatenated arrays, but only the new rows cross the boundary.  (The reference
+ * re-reads every trial on every call, service.go:62-69 + sample.go:98; trials never leave a goptuna study, so a
+ * history only grows.)  Needs a preceding kb_tpe_set_history (n_trials = 0 is fine). */
+int kb_tpe_append_history(kb_ctx *ctx, int64_t n_new, const double *values, const double *loss);
 
 /* Options of the TPE path.  KB_OPT_MERGE_DUPLICATES (default 0): components of an estimator that have identical
  * (mu, sigma) are folded into one with the summed weight before scoring.  The mixture is the same function (scores
  * agree to rounding) but has far fewer terms for integer / stepped parameters, whose histories are mostly repeats.
- * goptuna evaluates every observation separately; the default reproduces that count.  Takes effect at the next
- * kb_tpe_set_history.  kb_service_* switches it on. */
+ * goptuna evaluates every observation separately; the default reproduces that count.  Tables of a history already
+ * set are rebuilt at once.  kb_service_* switches it on. */
 #define KB_OPT_MERGE_DUPLICATES 1
 int kb_tpe_set_option(kb_ctx *ctx, int option, int value);
 
@@ -209,8 +214,16 @@ int kb_service_get_suggestions(kb_service *svc, const void *request, size_t requ
 int kb_service_validate_algorithm_settings(kb_service *svc, const void *request, size_t request_len);
 const char *kb_service_last_message(const kb_service *svc);
 /* Introspection for tests: 0 CMA-ES population size in use, 1 restarts so far (IPOP / BIPOP), 2 internal trials,
- * 3 generation tag, 4 Complete observations. */
+ * 3 generation tag, 4 Complete observations, 5 history rows sent to the GPU so far (kb_tpe_set_history +
+ * kb_tpe_append_history), 6 trials adopted under KB_SVC_ADOPT_UNKNOWN_TRIALS. */
 long long kb_service_stat(kb_service *svc, int which);
+/* KB_SVC_ADOPT_UNKNOWN_TRIALS (default 0): a trial whose parameters match no trial this service suggested fails
+ * GetSuggestions with "Same parameter is not found for Trial: <name>" in the reference (sample.go:126) -- which is
+ * what happens to every finished trial after the suggestion pod restarts, since the study lives in memory
+ * (service.go:39-52).  With the option on, such a trial joins the study and, once finished, the history.  A superset
+ * of the reference's behaviour, so it is off unless asked for. */
+#define KB_SVC_ADOPT_UNKNOWN_TRIALS 1
+int kb_service_set_option(kb_service *svc, int option, int value);
 
 /* ---- measurement helpers (used by bench.py and the profiles) ----------------------------------
  * which: 0 = MUFU.EX2 Gop/s, 1 = FP32 FFMA GFMA/s, 2 = FP64 DFMA GFMA/s, 3 = HBM write GB/s,

@@ -63,6 +63,7 @@ def lib():
         "kb_comm_world": ([vp, C.POINTER(i32), C.POINTER(i32)], i32),
         "kb_space_set": ([vp, i32, vp, vp, vp, vp, vp], i32),
         "kb_tpe_set_history": ([vp, i64, vp, vp], i32),
+        "kb_tpe_append_history": ([vp, i64, vp, vp], i32),
         "kb_tpe_set_option": ([vp, i32, i32], i32),
         "kb_tpe_get_parzen": ([vp, i32, i32, C.POINTER(i32), vp, vp, vp, i32, C.POINTER(dbl)], i32),
         "kb_tpe_scores": ([vp, i64, vp, vp], i32),
@@ -89,6 +90,7 @@ def lib():
         "kb_service_validate_algorithm_settings": ([vp, vp, C.c_size_t], i32),
         "kb_service_last_message": ([vp], C.c_char_p),
         "kb_service_stat": ([vp, i32], C.c_longlong),
+        "kb_service_set_option": ([vp, i32, i32], i32),
         "kb_profile": ([vp, i32], i32),
         "kb_profile_read": ([vp, i32, C.POINTER(dbl), C.POINTER(i64)], i32),
     }
@@ -148,6 +150,11 @@ class Service:
 
     def stat(self, which):
         return int(lib().kb_service_stat(self._h, which))
+
+    def set_option(self, option, value):
+        rc = lib().kb_service_set_option(self._h, option, value)
+        if rc:
+            raise KbError(rc, "kb_service_set_option: unknown option")
 
     def validate(self, request_bytes):
         """-> (grpc status code, status message); request_bytes None = nil request"""
@@ -237,6 +244,10 @@ class Context:
         values, loss = _f64(values), _f64(loss)
         n = len(loss)
         self._ck(lib().kb_tpe_set_history(self._h, n, _ptr(values), _ptr(loss)))
+
+    def tpe_append_history(self, values, loss):
+        values, loss = _f64(values), _f64(loss)
+        self._ck(lib().kb_tpe_append_history(self._h, len(loss), _ptr(values), _ptr(loss)))
 
     def tpe_get_parzen(self, param, side, cap=None):
         K = C.c_int()

@@ -262,6 +262,12 @@ struct kb_service {
     bool maximize = false;
     std::vector<InternalTrial> trials;
     std::map<std::string, int> mapping;  // Katib trial name -> internal trial id
+    // trials not yet claimed by a Katib name, by parameter set, ids ascending.  A trial leaves Running only through
+    // SyncTrials, i.e. after it was claimed, so every entry here is Running: the newest match is back().
+    std::map<std::map<std::string, double>, std::vector<int>> unclaimed;
+    std::vector<int> uploaded;  // trial ids whose rows are on the device as the TPE history, in row order
+    long long rows_uploaded = 0, adopted = 0;
+    bool adopt_unknown = false;  // KB_SVC_ADOPT_UNKNOWN_TRIALS
     bool history_dirty = true;
     uint64_t draw_counter = 0;
     // cmaes
@@ -406,15 +412,15 @@ static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &me
 }
 
 // findGoptunaTrialIDByParam (sample.go:97-127): newest unmapped Running trial with identical parameters
+// The reference scans a deep copy of every trial per look-up (O(N) each, O(N^2) for a cold sync); the index keyed by
+// the parameter set answers the same question -- same winner -- in O(log N).
 static int FindTrialByParams(kb_service *s, const ConvertedTrial &kt) {
-    std::set<int> mapped;
-    for (auto &m : s->mapping) mapped.insert(m.second);
-    for (size_t i = s->trials.size(); i-- > 0;) {
-        const InternalTrial &t = s->trials[i];
-        if (t.state != ST_RUNNING || mapped.count(t.id)) continue;
-        if (t.params == kt.params) return t.id;
-    }
-    return -1;
+    auto it = s->unclaimed.find(kt.params);
+    if (it == s->unclaimed.end() || it->second.empty()) return -1;
+    const int id = it->second.back();
+    it->second.pop_back();
+    if (it->second.empty()) s->unclaimed.erase(it);
+    return id;
 }
 
 static Status SyncTrials(kb_service *s, const std::vector<ConvertedTrial> &kts) {
@@ -423,7 +429,17 @@ static Status SyncTrials(kb_service *s, const std::vector<ConvertedTrial> &kts) 
         auto it = s->mapping.find(kt.name);
         if (it == s->mapping.end()) {
             id = FindTrialByParams(s, kt);
-            if (id < 0) return fail(GRPC_INTERNAL, "Same parameter is not found for Trial: " + kt.name);
+            if (id < 0) {
+                if (!s->adopt_unknown) return fail(GRPC_INTERNAL, "Same parameter is not found for Trial: " + kt.name);
+                // superset behaviour (off by default): a trial this process never suggested -- the pod restarted, or
+                // the trials come from a resumed experiment -- joins the study as a Running trial and is then synced
+                // like any other; it carries no CMA-ES generation tag, so it never enters a Tell
+                InternalTrial t;
+                t.id = id = (int)s->trials.size();
+                t.params = kt.params;
+                s->trials.push_back(t);
+                s->adopted++;
+            }
             s->mapping[kt.name] = id;
         } else id = it->second;
         InternalTrial &t = s->trials[(size_t)id];
@@ -443,19 +459,31 @@ static Status engine_error(kb_service *s, const char *what) {
 // upload Complete (and value-less Pruned, ranked last) trials as the TPE history
 static Status PushHistory(kb_service *s) {
     if (!s->history_dirty) return Status();
-    const size_t D = s->space.size();
-    std::vector<double> values, loss;
+    // observations in trial-id order, as study.GetTrials() returns them (the weight ramp and ties depend on the order)
+    std::vector<int> ids;
     for (const InternalTrial &t : s->trials) {
         if (t.state != ST_COMPLETE && t.state != ST_PRUNED) continue;
         bool all = true;
         for (const Param &p : s->space) if (!t.params.count(p.name)) all = false;
-        if (!all) continue;
+        if (all) ids.push_back(t.id);
+    }
+    // Only rows the device does not hold yet cross the boundary -- as long as the rows it holds are still a prefix of
+    // the ordered list (trials finishing out of order put a smaller id behind a larger one: then everything is resent).
+    size_t keep = 0;
+    if (!s->uploaded.empty() && s->uploaded.size() <= ids.size() && std::equal(s->uploaded.begin(), s->uploaded.end(), ids.begin()))
+        keep = s->uploaded.size();
+    std::vector<double> values, loss;
+    for (size_t i = keep; i < ids.size(); i++) {
+        const InternalTrial &t = s->trials[(size_t)ids[i]];
         for (const Param &p : s->space) values.push_back(t.params.at(p.name));
         loss.push_back(t.state == ST_COMPLETE ? (s->maximize ? -t.value : t.value) : INFINITY);
     }
-    if (kb_tpe_set_history(s->ctx, (int64_t)loss.size(), values.empty() ? nullptr : values.data(), loss.empty() ? nullptr : loss.data()))
-        return engine_error(s, "kb_tpe_set_history");
-    (void)D;
+    const int rc = keep > 0
+        ? kb_tpe_append_history(s->ctx, (int64_t)loss.size(), values.empty() ? nullptr : values.data(), loss.empty() ? nullptr : loss.data())
+        : kb_tpe_set_history(s->ctx, (int64_t)loss.size(), values.empty() ? nullptr : values.data(), loss.empty() ? nullptr : loss.data());
+    if (rc) { s->uploaded.clear(); return engine_error(s, keep > 0 ? "kb_tpe_append_history" : "kb_tpe_set_history"); }
+    s->uploaded = ids;
+    s->rows_uploaded += (long long)loss.size();
     s->history_dirty = false;
     return Status();
 }
@@ -658,6 +686,7 @@ static Status SampleNext(kb_service *s, std::vector<KV> &assignments) {
         assignments.push_back(a);
     }
     s->trials.push_back(t);
+    s->unclaimed[t.params].push_back(t.id);
     return Status();
 }
 
@@ -760,6 +789,15 @@ extern "C" long long kb_service_stat(kb_service *s, int which) {
         case 2: return (long long)s->trials.size();
         case 3: return s->cma_generation;
         case 4: { long long c = 0; for (const InternalTrial &t : s->trials) c += t.state == ST_COMPLETE; return c; }
+        case 5: return s->rows_uploaded;
+        case 6: return s->adopted;
         default: return -1;
     }
+}
+
+extern "C" int kb_service_set_option(kb_service *s, int option, int value) {
+    if (!s) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(s->mu);
+    if (option == KB_SVC_ADOPT_UNKNOWN_TRIALS) { s->adopt_unknown = value != 0; return KB_OK; }
+    return KB_ERR_INVALID;
 }

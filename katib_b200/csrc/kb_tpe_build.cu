@@ -400,25 +400,33 @@ int kb_tpe_free_history(kb_ctx *ctx) {
     return KB_OK;
 }
 
-extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss) {
-    if (!ctx) return KB_ERR_INVALID;
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    KbDeviceGuard g(ctx->device);
-    if (ctx->D == 0) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_set_history: call kb_space_set first");
-    if (n_trials < 0 || n_trials > (1 << 22))
-        return kb_fail(ctx, KB_ERR_UNSUPPORTED, "kb_tpe_set_history: n_trials=%lld outside [0, 2^22]", (long long)n_trials);
-    if (n_trials > 0 && (!values || !loss)) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_history: NULL buffer");
-    const int n = (int)n_trials, D = ctx->D;
+// Shared by kb_tpe_set_history (keep = 0) and kb_tpe_append_history (keep = the rows already on the device): rows
+// [keep, keep + n_add) come from the host, then every table is rebuilt from the whole device-resident history.
+static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_t n_add, const double *values,
+                            const double *loss) {
+    if (ctx->D == 0) return kb_fail(ctx, KB_ERR_STATE, "%s: call kb_space_set first", who);
+    if (n_add < 0 || keep64 + n_add > (1 << 22))
+        return kb_fail(ctx, KB_ERR_UNSUPPORTED, "%s: n_trials=%lld outside [0, 2^22]", who, (long long)(keep64 + n_add));
+    if (n_add > 0 && (!values || !loss)) return kb_fail(ctx, KB_ERR_INVALID, "%s: NULL buffer", who);
+    const int keep = (int)keep64, n = (int)(keep64 + n_add), D = ctx->D;
     cudaStream_t s = ctx->stream;
     ctx->history_ready = false;
 
     if (n > ctx->hist_cap) {
-        cudaFree(ctx->d_values); cudaFree(ctx->d_loss); cudaFree(ctx->d_pos);
+        double *old_values = ctx->d_values, *old_loss = ctx->d_loss;
+        cudaFree(ctx->d_pos);
         ctx->d_values = ctx->d_loss = nullptr; ctx->d_pos = nullptr;
         int64_t cap = n + n / 4 + 64;
+        ctx->hist_cap = 0;
         KB_CUDA(ctx, cudaMalloc(&ctx->d_values, sizeof(double) * (size_t)cap * D));
         KB_CUDA(ctx, cudaMalloc(&ctx->d_loss, sizeof(double) * (size_t)cap));
         KB_CUDA(ctx, cudaMalloc(&ctx->d_pos, sizeof(int32_t) * 2 * (size_t)cap));
+        if (keep > 0) {  // growing under an append: the rows already uploaded move over on the device
+            KB_CUDA(ctx, cudaStreamSynchronize(s));
+            KB_CUDA(ctx, cudaMemcpy(ctx->d_values, old_values, sizeof(double) * (size_t)keep * D, cudaMemcpyDeviceToDevice));
+            KB_CUDA(ctx, cudaMemcpy(ctx->d_loss, old_loss, sizeof(double) * (size_t)keep, cudaMemcpyDeviceToDevice));
+        }
+        cudaFree(old_values); cudaFree(old_loss);
         ctx->hist_cap = cap;
     }
     const int npad = next_pow2((int64_t)n + 1);
@@ -463,9 +471,10 @@ extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *v
         }
     }
     KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_dims, ctx->h_dims.data(), sizeof(KbDim) * (size_t)D, cudaMemcpyHostToDevice, s));
-    if (n > 0) {
-        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_values, values, sizeof(double) * (size_t)n * D, cudaMemcpyHostToDevice, s));
-        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_loss, loss, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, s));
+    if (n_add > 0) {
+        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_values + (size_t)keep * D, values, sizeof(double) * (size_t)n_add * D,
+                                     cudaMemcpyHostToDevice, s));
+        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_loss + keep, loss, sizeof(double) * (size_t)n_add, cudaMemcpyHostToDevice, s));
     }
     const int nb = [&] { int a = (int)ceil(0.1 * (double)n); return a > 25 ? 25 : a; }();
     split_kernel<<<1, BUILD_THREADS, 0, s>>>(ctx->d_loss, n, npad, ctx->d_sort_keys, ctx->d_sort_idx, ctx->d_pos);
@@ -500,6 +509,21 @@ extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *v
     ctx->n_below = nb;
     ctx->history_ready = true;
     return KB_OK;
+}
+
+extern "C" int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    return tpe_load_history(ctx, "kb_tpe_set_history", 0, n_trials, values, loss);
+}
+
+extern "C" int kb_tpe_append_history(kb_ctx *ctx, int64_t n_new, const double *values, const double *loss) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_append_history: no history set (call kb_tpe_set_history first)");
+    return tpe_load_history(ctx, "kb_tpe_append_history", ctx->n_trials, n_new, values, loss);
 }
 
 extern "C" int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, double *w, double *mu, double *sigma,
@@ -539,9 +563,11 @@ extern "C" int kb_tpe_set_option(kb_ctx *ctx, int option, int value) {
     if (!ctx) return KB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
     if (option == KB_OPT_MERGE_DUPLICATES) {
+        if (ctx->tpe_merge == (value != 0)) return KB_OK;
         ctx->tpe_merge = value != 0;
-        ctx->history_ready = false;  // tables must be rebuilt under the new setting
-        return KB_OK;
+        if (!ctx->history_ready) return KB_OK;
+        KbDeviceGuard g(ctx->device);  // tables are rebuilt under the new setting from the history on the device
+        return tpe_load_history(ctx, "kb_tpe_set_option", ctx->n_trials, 0, nullptr, nullptr);
     }
     return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_option: unknown option %d", option);
 }
