@@ -274,11 +274,6 @@ int kb_transpose(kb_ctx *ctx, int rows, int cols, const double *in, double *out,
 #define EG_THREADS 256
 #define EG_MAX_SWEEPS 40
 
-struct EighShared {   // device scalars
-    int rotated;      // rotations applied in the current sweep
-    int sweeps;
-};
-
 __device__ __forceinline__ double warp_sum(double v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
@@ -746,13 +741,19 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
                     chol_path = true;
                 }
             }
-            KB_CUDA(ctx, cudaFuncSetAttribute(jacobi_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            int blocks = NB / 2, per_sm = 0;
-            KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_block_kernel, JB_THREADS, smem));
-            const int cap = per_sm * ctx->prop.multiProcessorCount;
-            if (blocks > cap) blocks = cap;
-            void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv, &with_v};
-            KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_block_kernel, dim3((unsigned)blocks), dim3(JB_THREADS), args, smem, st));
+            bool gram = false;  // Gram-form block step (kb_eigh_gram.cu) when its columns fit; else the column-wise one
+            // the Cholesky panel buffer (32 n doubles) is free by now: it carries the per-block Gram diagonal blocks
+            int rcg = kb_jacobi_gram(ctx, n, Gt, Vt, colstep, sh, sweep_rot, Pt, tolv, with_v, EG_MAX_SWEEPS, st, &gram);
+            if (rcg) return rcg;
+            if (!gram) {
+                KB_CUDA(ctx, cudaFuncSetAttribute(jacobi_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                int blocks = NB / 2, per_sm = 0;
+                KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_block_kernel, JB_THREADS, smem));
+                const int cap = per_sm * ctx->prop.multiProcessorCount;
+                if (blocks > cap) blocks = cap;
+                void *args[] = {&n, &Gt, &Vt, &colstep, &sh, &sweep_rot, &tolv, &with_v};
+                KB_CUDA(ctx, cudaLaunchCooperativeKernel((void *)jacobi_block_kernel, dim3((unsigned)blocks), dim3(JB_THREADS), args, smem, st));
+            } else ctx->launches--;  // counted by kb_jacobi_gram
         } else {
             int blocks = pairs, per_sm = 0;
             KB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jacobi_flag_kernel, EF_THREADS, 0));

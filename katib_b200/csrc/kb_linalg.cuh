@@ -12,3 +12,12 @@ size_t kb_eigh_workspace_bytes(int n);
 // d_V0t (optional): warm start, transposed eigenvectors of a nearby matrix; sweeps_out (optional, host): sweeps used
 int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *d_w, double *d_V, void *workspace,
                    cudaStream_t st, const double *d_V0t, int *sweeps_out);
+
+struct EighShared {   // device scalars of one eigensolve
+    int rotated;      // rotations applied in the current sweep
+    int sweeps;
+};
+// Gram-form block step of the one-sided Jacobi iteration (kb_eigh_gram.cu); *launched = false when the resident
+// columns do not fit into shared memory; hblk: scratch of at least 8 * (n + 16) doubles
+int kb_jacobi_gram(kb_ctx *ctx, int n, double *Gt, double *Vt, int *blkstep, EighShared *sh, int *sweep_rot, double *hblk, double tol,
+                   int with_v, int max_sweeps, cudaStream_t st, bool *launched);
