@@ -316,8 +316,10 @@ class Context:
         self._cma_n = len(mean)
         self._ck(lib().kb_cmaes_create(self._h, len(mean), _ptr(mean), sigma, popsize, _ptr(lo_a), _ptr(hi_a)))
 
-    def cmaes_ask(self, lam, z=None, seed=0):
-        x = np.zeros((lam, self._cma_n))
+    def cmaes_ask(self, lam, z=None, seed=0, out=None):
+        """out: optional C-contiguous float64 [lam, n] buffer to receive x (e.g. a view of pinned memory)"""
+        x = out if out is not None else np.zeros((lam, self._cma_n))
+        assert x.dtype == np.float64 and x.flags.c_contiguous and x.shape == (lam, self._cma_n)
         zz = _f64(z) if z is not None else None
         self._ck(lib().kb_cmaes_ask(self._h, lam, _ptr(zz), seed, _ptr(x)))
         return x

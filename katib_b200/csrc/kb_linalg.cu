@@ -648,15 +648,34 @@ __global__ void eigh_order_kernel(int n, const double *__restrict__ Vt, const do
     const int j = blockIdx.x;  // source column
     __shared__ int s_rank;
     __shared__ double s_sign;
+    __shared__ double s_big[4];
+    __shared__ int s_at[4];
+    // rank = how many eigenvalues sort before this one; sign = that of the first component of largest magnitude
+    const double lj = lam[j];
+    int cnt = 0;
+    double big = 0.0;
+    int at = n;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+        const double le = lam[e];
+        cnt += (le < lj || (le == lj && e < j)) ? 1 : 0;
+        const double a = fabs(Vt[(size_t)j * n + e]);
+        if (a > big) { big = a; at = e; }  // ascending e per thread: the first maximum stays
+    }
+    if (threadIdx.x == 0) s_rank = 0;
+    __syncthreads();
+    for (int o = 16; o > 0; o >>= 1) {
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        const double ob = __shfl_xor_sync(0xffffffffu, big, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, at, o);
+        if (ob > big || (ob == big && oa < at)) { big = ob; at = oa; }
+    }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&s_rank, cnt); s_big[threadIdx.x >> 5] = big; s_at[threadIdx.x >> 5] = at; }
+    __syncthreads();
     if (threadIdx.x == 0) {
-        const double lj = lam[j];
-        int r = 0;
-        for (int e = 0; e < n; e++) { const double le = lam[e]; r += (le < lj || (le == lj && e < j)) ? 1 : 0; }
-        s_rank = r;
-        double big = 0.0, sv = 1.0;
-        for (int k = 0; k < n; k++) { const double v = Vt[(size_t)j * n + k]; if (fabs(v) > big) { big = fabs(v); sv = v < 0 ? -1.0 : 1.0; } }
-        s_sign = sv;
-        w[r] = lj;
+        for (int q = 1; q < (int)(blockDim.x >> 5); q++)
+            if (s_big[q] > big || (s_big[q] == big && s_at[q] < at)) { big = s_big[q]; at = s_at[q]; }
+        s_sign = (at < n && Vt[(size_t)j * n + at] < 0) ? -1.0 : 1.0;
+        w[s_rank] = lj;
     }
     __syncthreads();
     const int r = s_rank;
@@ -720,7 +739,10 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
                 KB_CUDA(ctx, cudaMemsetAsync(chol_fail, 0, sizeof(int), st));
                 KB_CUDA(ctx, cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                   (int)(sizeof(double) * (size_t)pw * n)));
-                for (int j0 = 0; j0 < n; j0 += pw) {
+                bool coop = false;  // single cooperative kernel (kb_chol.cu) when a 32-column panel fits in shared memory
+                int rcc = kb_chol_coop(ctx, n, Gt, chol_fail, st, &coop);
+                if (rcc) return rcc;
+                for (int j0 = coop ? n : 0; j0 < n; j0 += pw) {
                     const int w = std::min(pw, n - j0), m = n - j0;
                     chol_panel_kernel<<<1, CH_THREADS, sizeof(double) * (size_t)w * m, st>>>(n, j0, w, Gt, Pt, chol_fail);
                     KB_LAUNCH_CHECK(ctx);

@@ -17,6 +17,9 @@ struct EighShared {   // device scalars of one eigensolve
     int rotated;      // rotations applied in the current sweep
     int sweeps;
 };
+// In-place Cholesky factor of the symmetric matrix in Gt (column-contiguous), one cooperative kernel (kb_chol.cu);
+// *fail (device) is set when a pivot is not positive; *launched = false when a panel does not fit in shared memory
+int kb_chol_coop(kb_ctx *ctx, int n, double *Gt, int *fail, cudaStream_t st, bool *launched);
 // Gram-form block step of the one-sided Jacobi iteration (kb_eigh_gram.cu); *launched = false when the resident
 // columns do not fit into shared memory; hblk: scratch of at least 8 * (n + 16) doubles
 int kb_jacobi_gram(kb_ctx *ctx, int n, double *Gt, double *Vt, int *blkstep, EighShared *sh, int *sweep_rot, double *hblk, double tol,
