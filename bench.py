@@ -375,6 +375,9 @@ def main():
             a = ce_quant / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G CDF-pair evals/s (2 exp = 2 MUFU.EX2 each, algorithmic)", achieved=a,
                        peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2), traffic=198.6e6,
+                       note="frac > 1 is not an error: the peak is the SFU roofline of the erf formulation (2 exp per evaluation); "
+                            "on-grid components x on-grid candidates take the look-up class (1 LDS + 1 FFMA per evaluation, "
+                            "no SFU), which is bound by shared-memory load issue instead",
                        traffic_note="dram read+write bytes per launch (2^20-candidate chunk), ncu --set full, profiles/r01_ncu_tpe_score.md")
         if k == 0 and ms_k > 0:
             bytes_alg = float(n_local) * D * 8 * args.steps + float(n_local) * (n_cont * 8 + n_quant * 16) * args.steps

@@ -44,7 +44,14 @@ struct KbDim {
     float qf_h0[2];           // h0' = sqrt(log2 e) * q / (2 sqrt2 sigma_min)
     float qf_tau_s[2];        // 2 / (sqrt(log2 e) * KB_QF_YMAX)
     float qf_hw[2];           // normalised half bin width q_n / 2 the fit assumes
+    // ... and, of those, the components whose mu lies ON the quantisation grid (every observation of an integer /
+    // stepped parameter does): for a candidate on the grid the bin integral depends only on the integer offset
+    // k = (x - mu) / q, so it is a look-up in lut[side][k + G - 1], G = grid points, 2G - 1 entries (<= KB_LUT_MAX).
+    // The component's second float4 then carries (grid index * 128 + 64) as an integer in .w (0 = not this class).
+    float *lut[2];
+    int32_t lut_G[2];         // 0: class switched off for this (parameter, side)
 };
+#define KB_LUT_MAX 256        // floats per (parameter, side): grids of up to 128 points
 #ifndef KB_QF_DEG
 #define KB_QF_DEG 11
 #endif

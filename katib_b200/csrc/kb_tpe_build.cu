@@ -304,6 +304,19 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
         }
         if (!(worst < 1e-6)) dm.qf_h0[side] = -1.f;
     }
+    // look-up class (see KbDim::lut): bin integral of a floor-sigma component at every integer grid offset
+    int G = 0;
+    if (quant) {
+        const double gcount = (high - low) / dm.q;
+        const double gr = rint(gcount);
+        if (fabs(gcount - gr) <= 1e-9 * gcount && gr >= 1.0 && 2.0 * gr - 1.0 <= (double)KB_LUT_MAX) G = (int)gr;
+        const double rr = 1.0 / (sqrt(2.0) * minsigma2), h = 0.5 * dm.q * rr;
+        for (int k = tid; k < 2 * G - 1; k += nt) {
+            const double y = fabs((double)(k - (G - 1))) * dm.q * rr;
+            dm.lut[side][k] = (float)(erfc(y - h) - erfc(y + h));
+        }
+        if (tid == 0) dm.lut_G[side] = G;
+    }
     for (int j = tid; j < Kpad; j += nt) {
         float4 A, B;  // A = {-mu_hi, -mu_hi, s, s}  B = {-mu_lo*s, -mu_lo*s, t, t}
         if (j >= K) {
@@ -321,8 +334,13 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
                 const float wf = (float)w[j];
                 const float ws = sg[j] == minsigma2 ? -wf : wf;
                 const float mr = (float)(-ml * (double)r);
+                int code = 0;  // grid index of mu, pre-scaled to the look-up table's row pitch (128 B), +64 so that 0 = none
+                if (G > 0 && sg[j] == minsigma2) {
+                    const double gi = (mu[j] - (low + 0.5 * dm.q)) / dm.q, gr = rint(gi);
+                    if (fabs(gi - gr) <= 1e-9 && gr >= 0.0 && gr < (double)G) code = (int)gr * 128 + 64;
+                }
                 A = make_float4(-mh, -mh, r, r);
-                B = make_float4(mr, mr, ws, ws);
+                B = make_float4(mr, mr, ws, __int_as_float(code));
             } else {
                 double s = sg[j] > KB_EPS ? sg[j] : KB_EPS;
                 float c = (float)(sqrt(0.5 * LOG2E) * (high - low) / s);
@@ -444,7 +462,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
     for (int d = 0; d < D; d++) {
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
-        else bytes += 2 * (size_t)Kcap * (4 * sizeof(double) + 2 * sizeof(float4));
+        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 2 * sizeof(float4)) + KB_LUT_MAX * sizeof(float));
     }
     if (bytes > ctx->tabmem_bytes) {
         cudaFree(ctx->d_tabmem); ctx->d_tabmem = nullptr;
@@ -467,6 +485,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
                 k.sigma[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.logc[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
+                k.lut[side] = (float *)p; p += KB_LUT_MAX * sizeof(float);
             }
         }
     }

@@ -115,6 +115,9 @@ tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict
                         double mn = (0.5 * (ub + lb) - lo) * inv, hn = 0.5 * (ub - lb) * inv;
                         float mh = (float)mn, hwf = (float)hn;
                         float regular = fabs(hn - 0.5 * q * inv) <= 1e-9 * (q * inv) ? 1.f : 0.f;
+                        // a full bin centred ON the quantisation grid: .w = grid index + 2 (look-up class of the score kernel)
+                        const double gpos = (x - (lo + 0.5 * q)) / q, gidx = rint(gpos);
+                        if (regular != 0.f && fabs(gpos - gidx) <= 1e-9 && gidx >= 0.0 && gidx < 16384.0) regular = (float)(gidx + 2.0);
                         stage_quant[(size_t)slot * chunk_cap + row0 + r] = make_float4(mh, (float)(mn - (double)mh), hwf, regular);
                     } else {
                         double xn = (x - lo) * inv;
@@ -354,6 +357,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
                        const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
     __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
+    extern __shared__ __align__(128) float s_lut[];  // [2G - 1][32]: the current side's look-up table, one copy per bank
     const int slot = blockIdx.y;
     const int d = quant_dims[slot];
     const KbDim &dm = dims[d];
@@ -370,14 +374,22 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
         for (int c = 0; c < SC_STAGES && c < nchunks; c++) table_stream_issue(dm, c, nchunk0, s_tab[c], &s_bar[c]);
 
     float2 xm[SQ_R / 2], xl[SQ_R / 2], hw[SQ_R / 2];
-    bool all_regular = true;
+    bool all_regular = true, all_grid = true;
+    // look-up class: shared-memory address of this lane's copy of row (grid index + G - 1), +64 (see KbDim::lut);
+    // the table is replicated over the 32 banks (row pitch 128 B), so any mix of rows in a warp is conflict-free
+    uint32_t xo[SQ_R];
+    const int lutG = max(dm.lut_G[0], dm.lut_G[1]);
+    const uint32_t lut_lane = ((threadIdx.x & 31u) << 2) + 64u;  // byte offset into s_lut
 #pragma unroll
     for (int r = 0; r < SQ_R; r++) {
         int i = tile_base + r * SC_THREADS + threadIdx.x;
-        float4 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float4(0.5f, 0.f, dm.qf_hw[0], 1.f);
+        float4 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float4(0.5f, 0.f, dm.qf_hw[0], 2.f);
         if (r & 1) { xm[r / 2].y = v.x; xl[r / 2].y = v.y; hw[r / 2].y = v.z; }
         else { xm[r / 2].x = v.x; xl[r / 2].x = v.y; hw[r / 2].x = v.z; }
         all_regular = all_regular && v.w != 0.f;
+        const int gi = (int)v.w - 2;
+        all_grid = all_grid && gi >= 0 && gi < lutG;
+        xo[r] = lut_lane + ((uint32_t)(gi + lutG - 1) << 7);
     }
     float Shi[SQ_R], Slo[SQ_R];
     double P0[SQ_R];
@@ -386,7 +398,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
     const float qn = (float)(dm.q / (dm.hi - dm.lo));
     float2 qc[KB_QF_DEG + 1];
     float2 qnh0 = make_float2(0.f, 0.f), qts = make_float2(0.f, 0.f);
-    bool fast_ok = false;
+    bool fast_ok = false, grid_ok = false;
 
     for (int c = 0; c < nchunks; c++) {
         const int st = c % SC_STAGES;
@@ -395,12 +407,17 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
         const int cnt = min(SC_CHUNK, dm.Kpad[side] - cc * SC_CHUNK);
         mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
         const float4 *tab = s_tab[st];
-        if (cc == 0) {  // per-side constants of the fitted class
+        if (cc == 0) {  // per-side constants of the fitted class, and the side's look-up table
 #pragma unroll
             for (int i = 0; i <= KB_QF_DEG; i++) { const float v = dm.qf_coef[side][i]; qc[i] = make_float2(v, v); }
             qnh0 = make_float2(-dm.qf_h0[side], -dm.qf_h0[side]);
             qts = make_float2(dm.qf_tau_s[side], dm.qf_tau_s[side]);
             fast_ok = all_regular && dm.qf_h0[side] > 0.f;
+            // (every thread passed the barrier that closed the previous chunk, so the other side's table is dead)
+            const int rows = dm.lut_G[side] > 0 ? 2 * dm.lut_G[side] - 1 : 0;
+            for (int e = threadIdx.x; e < rows * 32; e += SC_THREADS) s_lut[e] = dm.lut[side][e >> 5];
+            grid_ok = all_grid && rows > 0;
+            __syncthreads();
         }
         for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
             float2 a32[SQ_R / 2];
@@ -408,9 +425,24 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
             for (int p = 0; p < SQ_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
 #pragma unroll 2
             for (int j = 0; j < SC_GROUP; j++) {
-                const float4 A = tab[2 * (j0 + j)], B = tab[2 * (j0 + j) + 1];
+                // the class is decided by the weight's sign and the grid code: one broadcast LDS.64; the other six
+                // floats of the entry are fetched only by the classes that do arithmetic on mu and sigma
+                const float2 Bzw = *reinterpret_cast<const float2 *>(&tab[2 * (j0 + j) + 1].z);
+                const float wj = fabsf(Bzw.x);
+                const uint32_t code = (uint32_t)__float_as_int(Bzw.y);
+                if (code != 0u && grid_ok) {
+                    // component and candidate both on the grid: one conflict-free LDS and one FFMA per evaluation
+#pragma unroll
+                    for (int r = 0; r < SQ_R; r++) {
+                        const float tv = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(s_lut) + (xo[r] - code));
+                        if (r & 1) a32[r / 2].y = fmaf(wj, tv, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, tv, a32[r / 2].x);
+                    }
+                    continue;
+                }
+                const float4 A = tab[2 * (j0 + j)];
+                const float2 Bxy = *reinterpret_cast<const float2 *>(&tab[2 * (j0 + j) + 1].x);
+                const float4 B = make_float4(Bxy.x, Bxy.y, Bzw.x, Bzw.y);
                 const float2 nmu = make_float2(A.x, A.y), rs = make_float2(A.z, A.w), ms = make_float2(B.x, B.y);
-                const float wj = fabsf(B.z);
                 if (B.z < 0.f && fast_ok) {
                     const float2 w2 = make_float2(wj, wj);
                     // Horner steps run across the four candidate pairs in lockstep: consecutive FFMA2s then share the
@@ -733,7 +765,10 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
     if (ctx->n_quant > 0) {
         dim3 grid((unsigned)((n + SQ_TILE - 1) / SQ_TILE), (unsigned)ctx->n_quant);
         KbProf pf(ctx, 2, s);
-        tpe_score_quant_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant, ctx->chunk_cap,
+        const size_t lut_bytes = (size_t)KB_LUT_MAX * 32 * sizeof(float);  // bank-replicated look-up table
+        // per device, and cheap: set on every launch rather than tracked (static 32 KB + dynamic 32 KB > the 48 KB default)
+        KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lut_bytes));
+        tpe_score_quant_kernel<<<grid, SC_THREADS, lut_bytes, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant, ctx->chunk_cap,
                                                            n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
     }

@@ -60,3 +60,29 @@ def test_service_uses_merged_tables_transparently():
         trials.append(_pb.trial(f"t{r}", a, "SUCCEEDED", [("loss", repr(f))]))
     assert svc.stat(4) == 39
     svc.close()
+
+
+@pytest.mark.parametrize("high,offgrid", [(63, False), (63, True), (199, False), (127, True)])
+def test_lookup_class_on_and_off_the_grid(high, offgrid):
+    """Quantised components and candidates that sit on the grid go through the look-up class of the score kernel;
+    candidates off the grid (legal through kb_tpe_scores), and grids of more than 128 points, must fall back to the
+    arithmetic classes.  Either way the scores are the oracle's."""
+    rng = np.random.Generator(np.random.PCG64(high + offgrid))
+    kinds, lows, highs, steps, nch = [kb.KB_INT, kb.KB_DISCRETE], [0, 1.0], [high, 9.0], [0, 0.125], [0, 0]
+    n = 1500
+    vals = make_history(rng, n, kinds, lows, highs, steps, nch)
+    loss = (vals[:, 0] - 0.3 * high) ** 2 / high + (vals[:, 1] - 4) ** 2 + rng.normal(0, 1.0, n)
+    sp = dict(kinds=kinds, lows=lows, highs=highs, steps=steps, nch=nch)
+    cand = sample_candidates(rng, 4096, sp, vals)
+    if offgrid:  # every 7th candidate a little off its grid point, so threads hold both kinds
+        cand[::7, 0] += 0.25
+        cand[3::7, 1] += 0.03
+    ref, best = oracle_scores(kinds, lows, highs, steps, nch, vals, loss, cand)
+    ctx = kb.Context(0)
+    ctx.space_set(kinds, lows, highs, steps, nch)
+    ctx.tpe_set_history(vals, loss)
+    got = ctx.tpe_scores(cand)
+    for d in range(2):
+        assert rel_err(got[:, d], ref[:, d]) < 1e-5, (d, rel_err(got[:, d], ref[:, d]))
+    assert list(ctx.tpe_score_select(cand)[0]) == best
+    ctx.close()
