@@ -399,6 +399,10 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
     float2 qc[KB_QF_DEG + 1];
     float2 qnh0 = make_float2(0.f, 0.f), qts = make_float2(0.f, 0.f);
     bool fast_ok = false, grid_ok = false;
+    float2 tvp[SQ_R / 2];      // look-up class: table values of the candidate pairs for grid code tv_code
+    uint32_t tv_code = 0u;
+#pragma unroll
+    for (int p = 0; p < SQ_R / 2; p++) tvp[p] = make_float2(0.f, 0.f);
 
     for (int c = 0; c < nchunks; c++) {
         const int st = c % SC_STAGES;
@@ -417,26 +421,61 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
             const int rows = dm.lut_G[side] > 0 ? 2 * dm.lut_G[side] - 1 : 0;
             for (int e = threadIdx.x; e < rows * 32; e += SC_THREADS) s_lut[e] = dm.lut[side][e >> 5];
             grid_ok = all_grid && rows > 0;
+            tv_code = 0u;  // the cached table values belong to the other side's table
             __syncthreads();
         }
         for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
             float2 a32[SQ_R / 2];
 #pragma unroll
             for (int p = 0; p < SQ_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
+            // Runs of components on ONE grid point (the rule in a dense history of an integer parameter: the table is
+            // sorted by mu) take a branch-free inner loop: one broadcast LDS of the weight and four packed FFMAs per
+            // component.  The group is cut into runs of equal grid code with one ballot per run.
+            const uint32_t cj = (uint32_t)__float_as_int(tab[2 * (j0 + (int)(threadIdx.x & 31u)) + 1].w);
+            for (int jb = 0, je; jb < SC_GROUP; jb = je) {
+                const uint32_t rcode = __shfl_sync(0xffffffffu, cj, jb);
+                const uint32_t eq = __ballot_sync(0xffffffffu, cj == rcode) >> jb;  // bit 0 = component jb itself
+                je = jb + (~eq == 0u ? 32 : __ffs((int)~eq) - 1);
+                if (rcode != 0u && grid_ok) {
+                    if (rcode != tv_code) {
+#pragma unroll
+                        for (int r = 0; r < SQ_R; r++) {
+                            const float tv = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(s_lut) + (xo[r] - rcode));
+                            if (r & 1) tvp[r / 2].y = tv; else tvp[r / 2].x = tv;
+                        }
+                        tv_code = rcode;
+                    }
+#pragma unroll 4
+                    for (int j = jb; j < je; j++) {
+                        const float wj = fabsf(tab[2 * (j0 + j) + 1].z);
+                        const float2 w2 = make_float2(wj, wj);
+#pragma unroll
+                        for (int p = 0; p < SQ_R / 2; p++) a32[p] = __ffma2_rn(w2, tvp[p], a32[p]);
+                    }
+                } else
 #pragma unroll 2
-            for (int j = 0; j < SC_GROUP; j++) {
+            for (int j = jb; j < je; j++) {
                 // the class is decided by the weight's sign and the grid code: one broadcast LDS.64; the other six
                 // floats of the entry are fetched only by the classes that do arithmetic on mu and sigma
                 const float2 Bzw = *reinterpret_cast<const float2 *>(&tab[2 * (j0 + j) + 1].z);
                 const float wj = fabsf(Bzw.x);
                 const uint32_t code = (uint32_t)__float_as_int(Bzw.y);
                 if (code != 0u && grid_ok) {
-                    // component and candidate both on the grid: one conflict-free LDS and one FFMA per evaluation
+                    // component and candidate both on the grid: the table value is fetched (one conflict-free LDS per
+                    // candidate) only when the component's grid point differs from the previous component's -- the
+                    // table is sorted by mu, so a dense history repeats each grid point many times in a row -- and
+                    // every (candidate, component) pair costs half a packed FFMA
+                    if (code != tv_code) {
 #pragma unroll
-                    for (int r = 0; r < SQ_R; r++) {
-                        const float tv = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(s_lut) + (xo[r] - code));
-                        if (r & 1) a32[r / 2].y = fmaf(wj, tv, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, tv, a32[r / 2].x);
+                        for (int r = 0; r < SQ_R; r++) {
+                            const float tv = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(s_lut) + (xo[r] - code));
+                            if (r & 1) tvp[r / 2].y = tv; else tvp[r / 2].x = tv;
+                        }
+                        tv_code = code;
                     }
+                    const float2 w2 = make_float2(wj, wj);
+#pragma unroll
+                    for (int p = 0; p < SQ_R / 2; p++) a32[p] = __ffma2_rn(w2, tvp[p], a32[p]);
                     continue;
                 }
                 const float4 A = tab[2 * (j0 + j)];
@@ -496,6 +535,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
                     }
                 }
             }
+            }  // runs of the group
 #pragma unroll
             for (int p = 0; p < SQ_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
