@@ -342,6 +342,23 @@ def main():
                   "components_above_per_param": k_merged,
                   "note": "identical mixture and winners; duplicate (mu, sigma) components of int/discrete parameters folded"}
         ctx.tpe_set_option(1, 0)
+    # ---- secondary: KB_OPT_PRUNE_FAR ("also report the pruned variant, roofline always from the
+    # algorithmic count"), alone and together with the merged tables; winners must not move
+    pruned = None
+    if os.environ.get("KB_BENCH_PRUNED", "1") == "1":
+        pruned = {}
+        for name, merge in (("prune_far", 0), ("prune_far+merge_duplicates", 1)):
+            ctx.tpe_set_option(1, merge)
+            ctx.tpe_set_option(2, 1)
+            for _ in range(min(2, args.warmup)):
+                step_dev()
+            ms_p, wall_p, res_p = timed(step_dev, args.steps)
+            assert np.array_equal(res[0], res_p[0]), f"{name}: winners differ from the unpruned run"
+            pruned[name] = {"value": n_total * args.steps / (ms_p * 1e-3), "unit": "candidates/s", "ms_per_step": ms_p / args.steps}
+        pruned["note"] = ("continuous parameters skip (candidate, component) pairs more than 7.75 floor-sigmas apart "
+                          "(< e^-30 of a component's peak); identical winners")
+        ctx.tpe_set_option(2, 0)
+        ctx.tpe_set_option(1, 0)
 
     def shutdown():
         # orderly exit on every rank: the library's NCCL communicator goes first, on all ranks together, then torch's
@@ -403,7 +420,7 @@ def main():
            "cpu_baseline": {"value": cpu_v, "unit": "candidates/s", "cores": cores, "kind": "port",
                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
-           "merged_duplicates": merged,
+           "merged_duplicates": merged, "pruned": pruned,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
     print(json.dumps(out), flush=True)
     shutdown()

@@ -50,6 +50,13 @@ struct KbDim {
     // The component's second float4 then carries (grid index * 128 + 64) as an integer in .w (0 = not this class).
     float *lut[2];
     int32_t lut_G[2];         // 0: class switched off for this (parameter, side)
+    // continuous parameters, KB_OPT_PRUNE_FAR: the same table split into the components whose sigma sits on the
+    // magic-clip floor ("narrow", still sorted by mu, Kn entries padded to KB_TABLE_PAD) and the rest ("wide", Kw
+    // entries, padded).  A narrow component further than prune_w (normalised) from a candidate contributes less than
+    // e^-30 of its own peak and is skipped; wide components (the prior, sparse regions) are always evaluated.
+    float4 *tabn[2], *tabw[2];
+    int32_t Kn[2], Kw[2];     // real counts; the tables are padded to KB_TABLE_PAD with zero-contribution entries
+    float prune_w[2];         // 7.75 sigma_floor of the side, normalised
 };
 #define KB_LUT_MAX 256        // floats per (parameter, side): grids of up to 128 points
 #ifndef KB_QF_DEG
@@ -118,6 +125,10 @@ struct kb_ctx {
     size_t tabmem_bytes = 0;
     bool history_ready = false;
     bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
+    bool tpe_prune = false;          // KB_OPT_PRUNE_FAR
+    float2 *d_stage_sorted = nullptr;  // [n_cont][chunk] stage_cont in bucket order (pruned scoring)
+    int32_t *d_perm = nullptr;         // [n_cont][chunk] chunk-local index of the candidate at each sorted position
+    int32_t *d_bucket = nullptr;       // [n_cont][KB_PRUNE_BUCKETS] histogram / running offsets
 
     // scoring scratch
     int64_t chunk_cap = 0;           // candidates per staged chunk

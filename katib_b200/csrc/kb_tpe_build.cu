@@ -352,6 +352,36 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
         tab[2 * j] = A;
         tab[2 * j + 1] = B;
     }
+    // KB_OPT_PRUNE_FAR (continuous parameters): the same entries split, in order, into floor-sigma ("narrow") and
+    // other ("wide") components -- see KbDim::tabn.  A stable partition by a block scan over per-thread segments.
+    if (!quant) {
+        __syncthreads();
+        const int seg = (K + nt - 1) / nt, b0 = min(K, tid * seg), b1 = min(K, b0 + seg);
+        int c = 0;
+        for (int j = b0; j < b1; j++) c += sg[j] == minsigma2 ? 1 : 0;
+        s_int[tid] = c;
+        __syncthreads();
+        for (int off = 1; off < nt; off <<= 1) {
+            int v = tid >= off ? s_int[tid - off] : 0;
+            __syncthreads();
+            s_int[tid] += v;
+            __syncthreads();
+        }
+        const int Kn = s_int[nt - 1], Kw = K - Kn;
+        int bn = s_int[tid] - c, bw = b0 - bn;
+        float4 *tn = dm.tabn[side], *tw = dm.tabw[side];
+        for (int j = b0; j < b1; j++) {
+            if (sg[j] == minsigma2) { tn[2 * bn] = tab[2 * j]; tn[2 * bn + 1] = tab[2 * j + 1]; bn++; }
+            else { tw[2 * bw] = tab[2 * j]; tw[2 * bw + 1] = tab[2 * j + 1]; bw++; }
+        }
+        const float4 Z = make_float4(0.f, 0.f, 0.f, 0.f), NI = make_float4(0.f, 0.f, -INFINITY, -INFINITY);
+        for (int j = Kn + tid; j < (Kn + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { tn[2 * j] = Z; tn[2 * j + 1] = NI; }
+        for (int j = Kw + tid; j < (Kw + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { tw[2 * j] = Z; tw[2 * j + 1] = NI; }
+        if (tid == 0) {
+            dm.Kn[side] = Kn; dm.Kw[side] = Kw;
+            dm.prune_w[side] = (float)(7.75 * minsigma2 * inv_range * (1.0 + 1e-6));
+        }
+    }
 }
 
 // ---- categorical parameters: weighted bincount (trial order) + prior weight, log ratio, ranks ------------
@@ -462,7 +492,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
     for (int d = 0; d < D; d++) {
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
-        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 2 * sizeof(float4)) + KB_LUT_MAX * sizeof(float));
+        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 6 * sizeof(float4)) + KB_LUT_MAX * sizeof(float));
     }
     if (bytes > ctx->tabmem_bytes) {
         cudaFree(ctx->d_tabmem); ctx->d_tabmem = nullptr;
@@ -481,6 +511,8 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
         } else {
             for (int side = 0; side < 2; side++) {
                 k.tab[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
+                k.tabn[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
+                k.tabw[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
                 k.mu[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.sigma[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
@@ -587,6 +619,10 @@ extern "C" int kb_tpe_set_option(kb_ctx *ctx, int option, int value) {
         if (!ctx->history_ready) return KB_OK;
         KbDeviceGuard g(ctx->device);  // tables are rebuilt under the new setting from the history on the device
         return tpe_load_history(ctx, "kb_tpe_set_option", ctx->n_trials, 0, nullptr, nullptr);
+    }
+    if (option == KB_OPT_PRUNE_FAR) {  // both table forms are always built: nothing to redo
+        ctx->tpe_prune = value != 0;
+        return KB_OK;
     }
     return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_option: unknown option %d", option);
 }

@@ -311,6 +311,248 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// KB_OPT_PRUNE_FAR, continuous parameters: candidates are bucketed by value (256 buckets over the normalised range, a
+// counting sort per chunk that keeps the chunk-local index), so that the 2048 candidates of a thread block span about
+// one bucket; the block then streams only the window of the mu-sorted floor-sigma table within 7.75 sigma of its
+// candidates, plus the (few) wide components.  Same arithmetic as tpe_score_cont_kernel on what it does evaluate.
+// ---------------------------------------------------------------------------------------------------------
+#define KB_PRUNE_BUCKETS 256
+#define BK_THREADS 256
+#define BK_ITEMS 8
+
+__device__ __forceinline__ int prune_bucket(float x) {
+    const int b = (int)(x * (float)KB_PRUNE_BUCKETS);
+    return b < 0 ? 0 : (b >= KB_PRUNE_BUCKETS ? KB_PRUNE_BUCKETS - 1 : b);
+}
+
+__global__ void __launch_bounds__(BK_THREADS)
+tpe_bucket_count_kernel(const float2 *__restrict__ stage, long long chunk_cap, int n, int *__restrict__ hist) {
+    __shared__ int s_h[KB_PRUNE_BUCKETS];
+    const int slot = blockIdx.y;
+    s_h[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < BK_ITEMS; it++) {
+        const int i = (blockIdx.x * BK_ITEMS + it) * BK_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&s_h[prune_bucket(stage[(size_t)slot * chunk_cap + i].x)], 1);
+    }
+    __syncthreads();
+    if (s_h[threadIdx.x]) atomicAdd(&hist[slot * KB_PRUNE_BUCKETS + threadIdx.x], s_h[threadIdx.x]);
+}
+
+__global__ void __launch_bounds__(KB_PRUNE_BUCKETS)
+tpe_bucket_scan_kernel(int *__restrict__ hist) {  // counts -> exclusive start offsets, in place; one block per parameter
+    __shared__ int s[KB_PRUNE_BUCKETS];
+    const int v = hist[blockIdx.x * KB_PRUNE_BUCKETS + threadIdx.x];
+    s[threadIdx.x] = v;
+    __syncthreads();
+    for (int off = 1; off < KB_PRUNE_BUCKETS; off <<= 1) {
+        const int a = threadIdx.x >= off ? s[threadIdx.x - off] : 0;
+        __syncthreads();
+        s[threadIdx.x] += a;
+        __syncthreads();
+    }
+    hist[blockIdx.x * KB_PRUNE_BUCKETS + threadIdx.x] = s[threadIdx.x] - v;
+}
+
+__global__ void __launch_bounds__(BK_THREADS)
+tpe_bucket_scatter_kernel(const float2 *__restrict__ stage, long long chunk_cap, int n, int *__restrict__ offs,
+                          float2 *__restrict__ sorted, int32_t *__restrict__ perm) {
+    __shared__ int s_cnt[KB_PRUNE_BUCKETS], s_base[KB_PRUNE_BUCKETS];
+    const int slot = blockIdx.y;
+    s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    float2 v[BK_ITEMS];
+    int b[BK_ITEMS], rk[BK_ITEMS];
+#pragma unroll
+    for (int it = 0; it < BK_ITEMS; it++) {
+        const int i = (blockIdx.x * BK_ITEMS + it) * BK_THREADS + threadIdx.x;
+        b[it] = -1;
+        if (i < n) {
+            v[it] = stage[(size_t)slot * chunk_cap + i];
+            b[it] = prune_bucket(v[it].x);
+            rk[it] = atomicAdd(&s_cnt[b[it]], 1);
+        }
+    }
+    __syncthreads();
+    s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&offs[slot * KB_PRUNE_BUCKETS + threadIdx.x], s_cnt[threadIdx.x]) : 0;
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < BK_ITEMS; it++) {
+        if (b[it] < 0) continue;
+        const int i = (blockIdx.x * BK_ITEMS + it) * BK_THREADS + threadIdx.x;
+        const size_t pos = (size_t)slot * chunk_cap + s_base[b[it]] + rk[it];
+        sorted[pos] = v[it];
+        perm[pos] = i;
+    }
+}
+
+struct PruneSeg { const float4 *p; int cnt; int c0; int nch; };  // table segment: entries (multiple of 32), first chunk, chunks
+
+__global__ void __launch_bounds__(SC_THREADS, 3)
+tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
+                             const float2 *__restrict__ sorted, const int32_t *__restrict__ perm, long long chunk_cap, int n,
+                             long long idx_base, int D, KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
+                             const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
+    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
+    __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
+    __shared__ PruneSeg s_seg[4];
+    __shared__ float s_lo[SC_THREADS / 32], s_hi[SC_THREADS / 32];
+    __shared__ float s_wmax[SC_THREADS / 32];
+    __shared__ float s_thr;
+    const int slot = blockIdx.y;
+    const int d = cont_dims[slot];
+    const KbDim &dm = dims[d];
+    const int tile_base = blockIdx.x * SC_TILE;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < SC_STAGES; s++) mbar_init(&s_bar[s], 1);
+        mbar_fence_init();
+    }
+    float2 xh[SC_R / 2], xl[SC_R / 2];
+    float lo = INFINITY, hi = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < SC_R; r++) {
+        const int i = tile_base + r * SC_THREADS + threadIdx.x;
+        float2 v = make_float2(0.5f, 0.f);
+        if (i < n) { v = sorted[(size_t)slot * chunk_cap + i]; lo = fminf(lo, v.x); hi = fmaxf(hi, v.x); }
+        if (r & 1) { xh[r / 2].y = v.x; xl[r / 2].y = v.y; } else { xh[r / 2].x = v.x; xl[r / 2].x = v.y; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+    __syncthreads();
+    if (threadIdx.x < 2) {  // one thread per side: window of the narrow table by binary search on mu (= -A.x)
+        const int side = threadIdx.x;
+        float bl = s_lo[0], bh = s_hi[0];
+        for (int w = 1; w < SC_THREADS / 32; w++) { bl = fminf(bl, s_lo[w]); bh = fmaxf(bh, s_hi[w]); }
+        const float W = dm.prune_w[side] + 2e-6f;  // + the FP32 split of candidate and mu
+        const float4 *tn = dm.tabn[side];
+        const int Kn = dm.Kn[side];
+        int a = 0, b = Kn;  // first j with mu_j >= bl - W
+        while (a < b) { const int m = (a + b) >> 1; if (-tn[2 * m].x < bl - W) a = m + 1; else b = m; }
+        const int j_lo = a;
+        b = Kn;             // first j with mu_j > bh + W
+        while (a < b) { const int m = (a + b) >> 1; if (-tn[2 * m].x <= bh + W) a = m + 1; else b = m; }
+        const int start = j_lo & ~(KB_TABLE_PAD - 1);
+        const int end = (a + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;  // <= padded Kn
+        PruneSeg sn, sw;
+        sn.p = tn + (size_t)2 * start; sn.cnt = bl <= bh ? end - start : 0;
+        sw.p = dm.tabw[side]; sw.cnt = (dm.Kw[side] + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
+        sn.nch = (sn.cnt + SC_CHUNK - 1) / SC_CHUNK; sw.nch = (sw.cnt + SC_CHUNK - 1) / SC_CHUNK;
+        sn.c0 = 0; sw.c0 = 0;
+        s_seg[2 * side] = sn; s_seg[2 * side + 1] = sw;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int c0 = 0;
+        for (int s = 0; s < 4; s++) { s_seg[s].c0 = c0; c0 += s_seg[s].nch; }
+    }
+    __syncthreads();
+    const int nchunks = s_seg[3].c0 + s_seg[3].nch;
+    const int side1_first = s_seg[2].c0;
+    auto issue = [&](int c, int st) {  // thread 0 only
+        int s = 0;
+        while (s < 3 && c >= s_seg[s].c0 + s_seg[s].nch) s++;
+        const int cc = c - s_seg[s].c0;
+        const int cnt = min(SC_CHUNK, s_seg[s].cnt - cc * SC_CHUNK);
+        const uint32_t bytes = (uint32_t)cnt * 2u * (uint32_t)sizeof(float4);
+        mbar_expect_tx(&s_bar[st], bytes);
+        tma_bulk_g2s(s_tab[st], s_seg[s].p + (size_t)cc * SC_CHUNK * 2, bytes, &s_bar[st]);
+    };
+    if (threadIdx.x == 0)
+        for (int c = 0; c < SC_STAGES && c < nchunks; c++) issue(c, c);
+
+    float Shi[SC_R], Slo[SC_R];
+    double logS0[SC_R];
+#pragma unroll
+    for (int r = 0; r < SC_R; r++) { Shi[r] = 0.f; Slo[r] = 0.f; logS0[r] = 0.0; }
+    for (int c = 0; c < nchunks; c++) {
+        const int st = c % SC_STAGES;
+        int s = 0;
+        while (s < 3 && c >= s_seg[s].c0 + s_seg[s].nch) s++;
+        const int cnt = min(SC_CHUNK, s_seg[s].cnt - (c - s_seg[s].c0) * SC_CHUNK);
+        mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
+        const float4 *tab = s_tab[st];
+        for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
+            float2 a32[SC_R / 2];
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
+#pragma unroll 4
+            for (int j = 0; j < SC_GROUP; j++) {
+                const float4 A = tab[2 * (j0 + j)], B = tab[2 * (j0 + j) + 1];
+                const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
+                const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) {
+                    float2 u = __fadd2_rn(xh[p], nmu);
+                    u = __fadd2_rn(u, xl[p]);
+                    const float2 t = __ffma2_rn(u, cs, ms);
+                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) {
+                two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
+                two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && c + SC_STAGES < nchunks) issue(c + SC_STAGES, st);
+        if (c == side1_first - 1) {
+#pragma unroll
+            for (int r = 0; r < SC_R; r++) {
+                logS0[r] = log((double)Shi[r] + (double)Slo[r]) + dm.L[0];
+                Shi[r] = 0.f; Slo[r] = 0.f;
+            }
+        }
+    }
+    // scores belong to the candidates' chunk-local indices perm[]; the block maximum / near-tie admission is that of
+    // select_publish, with the index indirection
+    float sc[SC_R];
+    int orig[SC_R];
+    float best = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < SC_R; r++) {
+        const double s64 = logS0[r] - (log((double)Shi[r] + (double)Slo[r]) + dm.L[1]);
+        sc[r] = (float)s64;
+        const int i = tile_base + r * SC_THREADS + threadIdx.x;
+        orig[r] = i < n ? perm[(size_t)slot * chunk_cap + i] : -1;
+        if (orig[r] >= 0) {
+            if (scores_out) scores_out[(size_t)orig[r] * D + d] = s64;
+            best = fmaxf(best, sc[r]);
+        }
+    }
+    if (!sel) return;
+    for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if ((threadIdx.x & 31) == 0) s_wmax[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float b = s_wmax[0];
+        for (int w = 1; w < SC_THREADS / 32; w++) b = fmaxf(b, s_wmax[w]);
+        const unsigned int mine = kb_f32_orderable(b);
+        const unsigned int old = atomicMax(&sel[d].gmax_bits, mine);
+        const float g = kb_f32_from_orderable(old > mine ? old : mine);
+        const float thr = g - KB_MARGIN_CONT * fmaxf(1.0f, fabsf(g));
+        s_thr = b >= thr ? thr : INFINITY;
+    }
+    __syncthreads();
+    const float thr = s_thr;
+    if (thr == INFINITY) return;
+    KbTie *ttab = tie + (size_t)dm.numeric_slot * slots;
+    float *tsc = tie_score + (size_t)dm.numeric_slot * slots;
+#pragma unroll
+    for (int r = 0; r < SC_R; r++) {
+        if (orig[r] >= 0 && sc[r] >= thr) {
+            const unsigned long long key = (unsigned long long)__double_as_longlong(cand_raw[(size_t)orig[r] * D + d]);
+            tie_insert(ttab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + orig[r]), sc[r]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // quantised parameters (q > 0): p(x) = sum_j w_j (Phi(ub) - Phi(lb)) per side.
 //
 // Table entry (same duplicated layout): A = {-mu_hi, -mu_hi, r', r'}  B = {-mu_lo*r', -mu_lo*r', +-w, +-w},
@@ -459,6 +701,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
                 // floats of the entry are fetched only by the classes that do arithmetic on mu and sigma
                 const float2 Bzw = *reinterpret_cast<const float2 *>(&tab[2 * (j0 + j) + 1].z);
                 const float wj = fabsf(Bzw.x);
+                if (wj == 0.f) continue;  // padding entry
                 const uint32_t code = (uint32_t)__float_as_int(Bzw.y);
                 if (code != 0u && grid_ok) {
                     // component and candidate both on the grid: the table value is fetched (one conflict-free LDS per
@@ -722,6 +965,8 @@ int kb_tpe_free(kb_ctx *ctx) {
     ctx->d_stage_cont = nullptr; ctx->d_stage_quant = nullptr; ctx->d_scores_chunk = nullptr;
     ctx->d_sel = nullptr; ctx->d_tie = nullptr; ctx->d_win = nullptr; ctx->d_win_all = nullptr;
     ctx->chunk_cap = 0;
+    cudaFree(ctx->d_stage_sorted); cudaFree(ctx->d_perm); cudaFree(ctx->d_bucket);
+    ctx->d_stage_sorted = nullptr; ctx->d_perm = nullptr; ctx->d_bucket = nullptr;
     cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
     cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list); cudaFree(ctx->d_tie_count); cudaFree(ctx->d_slot_of_dim); cudaFree(ctx->d_numeric_dims);
     if (ctx->h_win) cudaFreeHost(ctx->h_win);
@@ -767,6 +1012,8 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
         }
     }
     if (rows > ctx->chunk_cap) {
+        cudaFree(ctx->d_stage_sorted); cudaFree(ctx->d_perm);  // sized by chunk_cap; re-made on demand by the pruned path
+        ctx->d_stage_sorted = nullptr; ctx->d_perm = nullptr;
         cudaFree(ctx->d_stage_cont); cudaFree(ctx->d_stage_quant);
         for (int i = 0; i < 2; i++) { cudaFree(ctx->d_cand_chunk[i]); ctx->d_cand_chunk[i] = nullptr; }
         cudaFree(ctx->d_scores_chunk);
@@ -795,7 +1042,27 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
                                                                         sc->d_slot_of_dim, sel, local_base, d_scores);
     }
     KB_LAUNCH_CHECK(ctx);
-    if (ctx->n_cont > 0) {
+    if (ctx->n_cont > 0 && ctx->tpe_prune) {
+        const size_t per = (size_t)ctx->chunk_cap * (size_t)ctx->n_cont;
+        if (!ctx->d_stage_sorted) KB_CUDA(ctx, cudaMalloc(&ctx->d_stage_sorted, sizeof(float2) * per));
+        if (!ctx->d_perm) KB_CUDA(ctx, cudaMalloc(&ctx->d_perm, sizeof(int32_t) * per));
+        if (!ctx->d_bucket) KB_CUDA(ctx, cudaMalloc(&ctx->d_bucket, sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont));
+        KbProf pf(ctx, 1, s);
+        KB_CUDA(ctx, cudaMemsetAsync(ctx->d_bucket, 0, sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont, s));
+        dim3 bgrid((unsigned)((n + BK_THREADS * BK_ITEMS - 1) / (BK_THREADS * BK_ITEMS)), (unsigned)ctx->n_cont);
+        tpe_bucket_count_kernel<<<bgrid, BK_THREADS, 0, s>>>(ctx->d_stage_cont, ctx->chunk_cap, n, ctx->d_bucket);
+        KB_LAUNCH_CHECK(ctx);
+        tpe_bucket_scan_kernel<<<(unsigned)ctx->n_cont, KB_PRUNE_BUCKETS, 0, s>>>(ctx->d_bucket);
+        KB_LAUNCH_CHECK(ctx);
+        tpe_bucket_scatter_kernel<<<bgrid, BK_THREADS, 0, s>>>(ctx->d_stage_cont, ctx->chunk_cap, n, ctx->d_bucket,
+                                                              ctx->d_stage_sorted, ctx->d_perm);
+        KB_LAUNCH_CHECK(ctx);
+        dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
+        tpe_score_cont_pruned_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
+                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score,
+                                                                 ctx->tie_slots, d_cand, d_scores);
+        KB_LAUNCH_CHECK(ctx);
+    } else if (ctx->n_cont > 0) {
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
         KbProf pf(ctx, 1, s);
         tpe_score_cont_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont, ctx->chunk_cap, n,

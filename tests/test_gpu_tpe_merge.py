@@ -86,3 +86,39 @@ def test_lookup_class_on_and_off_the_grid(high, offgrid):
         assert rel_err(got[:, d], ref[:, d]) < 1e-5, (d, rel_err(got[:, d], ref[:, d]))
     assert list(ctx.tpe_score_select(cand)[0]) == best
     ctx.close()
+
+
+KB_OPT_PRUNE_FAR = 2
+
+
+@pytest.mark.parametrize("n_trials,n_cand,clustered", [(3000, 40000, False), (3000, 5000, True), (30, 3000, False),
+                                                       (1, 100, False), (12000, 2100, False)])
+def test_pruned_continuous_scoring_matches_unpruned(n_trials, n_cand, clustered):
+    """KB_OPT_PRUNE_FAR skips (candidate, component) pairs more than 7.75 floor-sigmas apart: scores move by less than
+    1e-6 relative, winners (decided in FP64 on the full mixture) not at all."""
+    rng = np.random.Generator(np.random.PCG64(n_trials + n_cand))
+    sp = MIXED
+    vals = make_history(rng, n_trials, sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    if n_trials >= 3000:  # a dense region and a sparse one: narrow and wide components both
+        vals[: n_trials // 2, 0] = rng.uniform(0.0, 0.4, n_trials // 2)
+    loss = (vals[:, 0] - 1.0) ** 2 + 0.05 * (vals[:, 1] - 3) ** 2 + rng.normal(0, 0.5, n_trials)
+    cand = sample_candidates(rng, n_cand, sp, vals)
+    if clustered:
+        cand[:, 0] = 0.2 + 1e-4 * rng.uniform(size=n_cand)
+        cand[:, 5] = sp["lows"][5]  # all on the lower edge
+    ctx = kb.Context(0)
+    ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    ctx.tpe_set_history(vals, loss)
+    s0, i0 = ctx.tpe_scores(cand), ctx.tpe_score_select(cand, index_offset=7)[0]
+    ctx.tpe_set_option(KB_OPT_PRUNE_FAR, 1)
+    s1, i1 = ctx.tpe_scores(cand), ctx.tpe_score_select(cand, index_offset=7)[0]
+    ctx.tpe_set_option(KB_OPT_PRUNE_FAR, 0)
+    s2 = ctx.tpe_scores(cand)
+    ctx.close()
+    assert np.array_equal(s0, s2)
+    for d, k in enumerate(sp["kinds"]):
+        assert rel_err(s1[:, d], s0[:, d]) < 1e-6, (d, rel_err(s1[:, d], s0[:, d]))
+    assert np.array_equal(i0, i1)
+    if n_trials <= 3000 and n_cand <= 5000:
+        ref, best = oracle_scores(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"], vals, loss, cand)
+        assert list(i1 - 7) == best
