@@ -262,47 +262,62 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     double dd2 = 1.0 + (double)K0;
     if (dd2 > 100.0) dd2 = 100.0;
     const double minsigma2 = 1.0 * (high - low) / dd2;  // the magic-clip floor (same expression as above)
-    if (quant && tid == 0) {
-        // fit R(tau) = log2( erfcx(y-h) - e^{-4yh} erfcx(y+h) ) on y in [0, YMAX] by interpolation at M Chebyshev nodes
+    if (quant) {
+        // fit R(tau) = log2( erfcx(y-h) - e^{-4yh} erfcx(y+h) ) on y in [0, YMAX] by interpolation at M Chebyshev nodes.
+        // Spread over the block (this sits on the latency path of every GetSuggestions: one thread doing all of it
+        // took ~0.2 ms): node values by M threads, Chebyshev coefficients by N+1 threads, the basis change by one.
         const int N = KB_QF_DEG, M = 40;
         const double h = dm.q / (2.0 * sqrt(2.0) * minsigma2);
-        double cheb[KB_QF_DEG + 1];
-        for (int nn = 0; nn <= N; nn++) cheb[nn] = 0.0;
-        for (int k = 0; k < M; k++) {
-            const double th = M_PI * ((double)k + 0.5) / (double)M;
+        __syncthreads();  // s_red is free again
+        if (tid < M) {
+            const double th = M_PI * ((double)tid + 0.5) / (double)M;
             const double y = (cos(th) + 1.0) * (KB_QF_YMAX / 2.0);
-            const double f = log2(erfcx(y - h) - exp(-4.0 * y * h) * erfcx(y + h));
-            for (int nn = 0; nn <= N; nn++) cheb[nn] += f * cos((double)nn * th);
+            s_red[tid] = log2(erfcx(y - h) - exp(-4.0 * y * h) * erfcx(y + h));
         }
-        for (int nn = 0; nn <= N; nn++) cheb[nn] *= (nn == 0 ? 1.0 : 2.0) / (double)M;
-        // Chebyshev -> monomial: T0 = 1, T1 = x, T_{n+1} = 2 x T_n - T_{n-1}
-        double mono[KB_QF_DEG + 1], tp[KB_QF_DEG + 1], tc[KB_QF_DEG + 1], tn[KB_QF_DEG + 1];
-        for (int i = 0; i <= N; i++) { mono[i] = 0.0; tp[i] = 0.0; tc[i] = 0.0; }
-        tp[0] = 1.0; tc[1] = 1.0;
-        mono[0] += cheb[0];
-        for (int i = 0; i <= N; i++) mono[i] += cheb[1] * tc[i];
-        for (int nn = 2; nn <= N; nn++) {
-            for (int i = 0; i <= N; i++) tn[i] = (i > 0 ? 2.0 * tc[i - 1] : 0.0) - tp[i];
-            for (int i = 0; i <= N; i++) { mono[i] += cheb[nn] * tn[i]; tp[i] = tc[i]; tc[i] = tn[i]; }
+        __syncthreads();
+        if (tid <= N) {
+            double c = 0.0;
+            for (int k = 0; k < M; k++) c += s_red[k] * cos((double)tid * (M_PI * ((double)k + 0.5) / (double)M));
+            s_red[64 + tid] = c * (tid == 0 ? 1.0 : 2.0) / (double)M;
         }
-        for (int i = 0; i < 16; i++) dm.qf_coef[side][i] = i <= N ? (float)mono[i] : 0.f;
-        dm.qf_h0[side] = (float)(sqrt(LOG2E) * h);
-        dm.qf_tau_s[side] = (float)(2.0 / (sqrt(LOG2E) * KB_QF_YMAX));
-        dm.qf_hw[side] = (float)(0.5 * dm.q * inv_range);
-    }
-    // self-check of the fit (quantised only): the fast path is switched off (h0 <= 0) when the interpolant misses
-    // the exact bin integral by more than 1e-6 anywhere on a 3x finer grid (happens for bins much wider than sigma)
-    if (quant && tid == 0) {
-        const double h = dm.q / (2.0 * sqrt(2.0) * minsigma2);
-        double worst = 0.0;
-        for (int k = 0; k <= 128; k++) {
-            const double y = KB_QF_YMAX * (double)k / 128.0, tau = 2.0 * y / KB_QF_YMAX - 1.0;
+        __syncthreads();
+        if (tid == 0) {
+            // Chebyshev -> monomial: T0 = 1, T1 = x, T_{n+1} = 2 x T_n - T_{n-1}
+            const double *cheb = s_red + 64;
+            double mono[KB_QF_DEG + 1], tp[KB_QF_DEG + 1], tc[KB_QF_DEG + 1], tn[KB_QF_DEG + 1];
+            for (int i = 0; i <= N; i++) { mono[i] = 0.0; tp[i] = 0.0; tc[i] = 0.0; }
+            tp[0] = 1.0; tc[1] = 1.0;
+            mono[0] += cheb[0];
+            for (int i = 0; i <= N; i++) mono[i] += cheb[1] * tc[i];
+            for (int nn = 2; nn <= N; nn++) {
+                for (int i = 0; i <= N; i++) tn[i] = (i > 0 ? 2.0 * tc[i - 1] : 0.0) - tp[i];
+                for (int i = 0; i <= N; i++) { mono[i] += cheb[nn] * tn[i]; tp[i] = tc[i]; tc[i] = tn[i]; }
+            }
+            for (int i = 0; i < 16; i++) dm.qf_coef[side][i] = i <= N ? (float)mono[i] : 0.f;
+            dm.qf_h0[side] = (float)(sqrt(LOG2E) * h);
+            dm.qf_tau_s[side] = (float)(2.0 / (sqrt(LOG2E) * KB_QF_YMAX));
+            dm.qf_hw[side] = (float)(0.5 * dm.q * inv_range);
+        }
+        __syncthreads();
+        // self-check of the fit: the fast path is switched off (h0 <= 0) when the interpolant misses the exact bin
+        // integral by more than 1e-6 anywhere on a 3x finer grid (happens for bins much wider than sigma)
+        double err = 0.0;
+        if (tid <= 128) {
+            const double y = KB_QF_YMAX * (double)tid / 128.0, tau = 2.0 * y / KB_QF_YMAX - 1.0;
             double pv = (double)dm.qf_coef[side][KB_QF_DEG];
             for (int i = KB_QF_DEG - 1; i >= 0; i--) pv = pv * tau + (double)dm.qf_coef[side][i];
             const double exact = log2(erfcx(y - h) - exp(-4.0 * y * h) * erfcx(y + h));
-            worst = fmax(worst, fabs(exp2(pv - exact) - 1.0));
+            err = fabs(exp2(pv - exact) - 1.0);
+            if (!(err == err)) err = INFINITY;  // NaN fails the check
         }
-        if (!(worst < 1e-6)) dm.qf_h0[side] = -1.f;
+        s_red[tid] = err;
+        __syncthreads();
+        for (int off = nt >> 1; off > 0; off >>= 1) {
+            if (tid < off) s_red[tid] = fmax(s_red[tid], s_red[tid + off]);
+            __syncthreads();
+        }
+        if (tid == 0 && !(s_red[0] < 1e-6)) dm.qf_h0[side] = -1.f;
+        __syncthreads();
     }
     // look-up class (see KbDim::lut): bin integral of a floor-sigma component at every integer grid offset
     int G = 0;

@@ -23,7 +23,10 @@
 // one wins -- the "identical selected candidate" rule of the parity contract.
 #include <math.h>
 
+#include <algorithm>
+
 #include "kb_internal.cuh"
+#include "kb_tpe_sample.cuh"
 
 #define KB_EPS 1e-12
 // Admission margin of the near-tie table, relative to max(1, |score|): several times the largest FP32
@@ -939,6 +942,78 @@ tpe_pick_kernel(const KbDim *__restrict__ dims, const KbSelect *__restrict__ sel
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// The latency path of kb_tpe_suggest (Katib's real shape: 24 EI candidates, tens to hundreds of trials): ONE kernel,
+// one CTA per parameter, that draws the candidates (the same Philox stream as tpe_sample_kernel), scores each in FP64
+// in the oracle's formula order (rescore_value -- what the big path falls back to for its near ties) and picks the
+// best, lowest index first.  Same winners as the staged pipeline, one launch and one 24 B x D read-back instead of a
+// dozen stream operations.
+// ---------------------------------------------------------------------------------------------------------
+#define SM_THREADS 256
+#define SM_MAX_CAND 1024
+__global__ void __launch_bounds__(SM_THREADS)
+tpe_suggest_small_kernel(const KbDim *__restrict__ dims, int n, uint64_t seed, KbWinner *__restrict__ win) {
+    __shared__ double s_x[SM_MAX_CAND], s_sc[SM_MAX_CAND];
+    __shared__ double s_bs[SM_THREADS];
+    __shared__ int s_bi[SM_THREADS];
+    const int d = blockIdx.x;
+    const KbDim &dm = dims[d];
+    const Philox ph(seed);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < n; i += SM_THREADS) {
+        const double x = tpe_sample_one(dm, ph, (unsigned long long)i, d);
+        s_x[i] = x;
+        if (dm.kind == KB_CATEGORICAL) {
+            int c = (int)x;
+            c = c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c);
+            s_sc[i] = dm.cat_score[c];
+        }
+    }
+    __syncthreads();
+    if (dm.kind != KB_CATEGORICAL) {
+        for (int i = warp; i < n; i += SM_THREADS / 32) {
+            const double v = rescore_value(dm, s_x[i], lane);
+            if (lane == 0) s_sc[i] = v;
+        }
+        __syncthreads();
+    }
+    double bs = -INFINITY;
+    int bi = n;
+    for (int i = threadIdx.x; i < n; i += SM_THREADS) {  // ascending i per thread: ">" keeps the first maximum
+        const double v = s_sc[i];
+        if (bi == n || v > bs) { bs = v; bi = i; }
+    }
+    s_bs[threadIdx.x] = bs; s_bi[threadIdx.x] = bi;
+    __syncthreads();
+    for (int off = SM_THREADS / 2; off > 0; off >>= 1) {
+        if (threadIdx.x < off) {
+            const double os = s_bs[threadIdx.x + off];
+            const int oi = s_bi[threadIdx.x + off];
+            if (oi < n && (s_bi[threadIdx.x] == n || os > s_bs[threadIdx.x] || (os == s_bs[threadIdx.x] && oi < s_bi[threadIdx.x]))) {
+                s_bs[threadIdx.x] = os; s_bi[threadIdx.x] = oi;
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        KbWinner w;
+        const int b = s_bi[0];
+        w.score = s_bs[0];
+        w.index = b < n ? (long long)b : -1;
+        double v = b < n ? s_x[b] : 0.0;
+        if (dm.kind == KB_DISCRETE) {  // sampleDiscreteUniform: shift back and clamp
+            v = v + dm.shift;
+            v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
+        }
+        if (dm.kind == KB_CATEGORICAL) {
+            int c = (int)v;
+            v = (double)(c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c));
+        }
+        w.value = v;
+        win[d] = w;
+    }
+}
+
 // pick the best of `world` gathered winner rows (score desc, index asc)
 __global__ void tpe_merge_kernel(const KbWinner *__restrict__ all, int world, int D, KbWinner *win) {
     const int d = blockIdx.x * blockDim.x + threadIdx.x;
@@ -983,11 +1058,11 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
     const int D = ctx->D;
     if (!ctx->d_sel) {
         KB_CUDA(ctx, cudaMalloc(&ctx->d_sel, sizeof(KbSelect) * (size_t)D));
-        KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)D));
+        if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)D));  // the small path may have made these two
         KB_CUDA(ctx, cudaMalloc(&ctx->d_win_all, sizeof(KbWinner) * (size_t)D * 64));
         const size_t slots = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
         KB_CUDA(ctx, cudaMalloc(&ctx->d_tie_count, sizeof(unsigned int) * slots));
-        KB_CUDA(ctx, cudaMallocHost(&sc->h_win, sizeof(KbWinner) * (size_t)D));
+        if (!sc->h_win) KB_CUDA(ctx, cudaMallocHost(&sc->h_win, sizeof(KbWinner) * (size_t)D));
         std::vector<int> slot_of((size_t)D, 0), numeric(slots, 0);
         for (int i = 0; i < ctx->n_cont; i++) slot_of[(size_t)ctx->cont_dims[(size_t)i]] = i;
         for (int i = 0; i < ctx->n_quant; i++) slot_of[(size_t)ctx->quant_dims[(size_t)i]] = i;
@@ -1226,6 +1301,29 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
     if (!out_value) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest: out_value is NULL");
     cudaStream_t s = ctx->stream;
     const int64_t n = n_ei_candidates;
+    {   // small problems (Katib's own: 24 candidates): the fused single-kernel path
+        int world = 1, rank = 0;
+        kb_comm_world(ctx, &world, &rank);
+        int64_t kmax = 1;
+        for (int d = 0; d < ctx->D; d++) {
+            const KbDim &k = ctx->h_dims[(size_t)d];
+            if (k.kind != KB_CATEGORICAL) kmax = std::max<int64_t>(kmax, (int64_t)k.K[0] + k.K[1]);
+        }
+        const char *off = getenv("KB_SUGGEST_SMALL");
+        if (world == 1 && n <= SM_MAX_CAND && n * kmax <= (1 << 18) && !(off && off[0] == '0')) {
+            if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)ctx->D));
+            if (!ctx->h_win) KB_CUDA(ctx, cudaMallocHost(&ctx->h_win, sizeof(KbWinner) * (size_t)ctx->D));
+            {
+                KbProf pf(ctx, 3, s);
+                tpe_suggest_small_kernel<<<(unsigned)ctx->D, SM_THREADS, 0, s>>>(ctx->d_dims, (int)n, seed, ctx->d_win);
+                KB_LAUNCH_CHECK(ctx);
+            }
+            KB_CUDA(ctx, cudaMemcpyAsync(ctx->h_win, ctx->d_win, sizeof(KbWinner) * (size_t)ctx->D, cudaMemcpyDeviceToHost, s));
+            KB_CUDA(ctx, cudaStreamSynchronize(s));
+            for (int d = 0; d < ctx->D; d++) out_value[d] = ctx->h_win[d].value;
+            return KB_OK;
+        }
+    }
     if (n * ctx->D > ctx->suggest_cap) {
         cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
         KB_CUDA(ctx, cudaMalloc(&ctx->d_suggest, sizeof(double) * (size_t)n * ctx->D));

@@ -98,3 +98,25 @@ def test_random_fill_ranges_and_uniformity(ctx):
         else:
             g = (x - lo) / st
             assert np.allclose(g, np.round(g)) and x.min() >= lo and x.max() <= hi
+
+
+@pytest.mark.parametrize("n_trials,n_cand", [(12, 24), (100, 24), (100, 1), (400, 300), (2000, 100)])
+def test_fused_small_suggest_equals_the_staged_pipeline(n_trials, n_cand, monkeypatch):
+    """kb_tpe_suggest takes a single fused kernel for small problems (FP64 scoring of every candidate); the staged
+    pipeline (FP32 scoring + FP64 re-scoring of the near ties) must pick the same values from the same Philox draws."""
+    import katib_b200 as kb
+    from test_gpu_tpe import MIXED, make_history
+    rng = np.random.Generator(np.random.PCG64(n_trials * 31 + n_cand))
+    sp = MIXED
+    vals = make_history(rng, n_trials, sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    loss = (vals[:, 0] - 1.0) ** 2 + 0.05 * (vals[:, 1] - 3) ** 2 + (vals[:, 2] != 1) + rng.normal(0, 0.5, n_trials)
+    ctx = kb.Context(0)
+    ctx.space_set(sp["kinds"], sp["lows"], sp["highs"], sp["steps"], sp["nch"])
+    ctx.tpe_set_history(vals, loss)
+    for seed in (1, 2, 3, 99):
+        monkeypatch.setenv("KB_SUGGEST_SMALL", "1")
+        a = ctx.tpe_suggest(n_cand, seed)
+        monkeypatch.setenv("KB_SUGGEST_SMALL", "0")
+        b = ctx.tpe_suggest(n_cand, seed)
+        assert np.array_equal(a, b), (seed, a, b)
+    ctx.close()
