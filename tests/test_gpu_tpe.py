@@ -205,8 +205,11 @@ def test_config5_shape_reduced(ctx):
     assert list(idx) == best
 
 
-def test_multi_chunk_host_path_and_offsets(ctx):
-    """2.5 Mi candidates cross the 2^20-row chunk boundary (double-buffered H2D): winners and indices vs the oracle."""
+def test_multi_chunk_host_path_and_offsets(monkeypatch):
+    """2.5 Mi candidates cross the chunk boundary three times (double-buffered H2D; chunks of 2^20 rows forced on a
+    fresh context, the default is 2^22): winners and indices vs the oracle."""
+    monkeypatch.setenv("KB_CHUNK_LOG2", "20")
+    ctx = kb.Context(0)
     rng = np.random.Generator(np.random.PCG64(8))
     ctx.space_set([kb.KB_UNIFORM, kb.KB_INT, kb.KB_CATEGORICAL], [0.0, 0, 0], [1.0, 9, 0], None, [0, 0, 4])
     n = 60
@@ -221,6 +224,10 @@ def test_multi_chunk_host_path_and_offsets(ctx):
     _, b2 = O.tpe_score_categorical(cand[:, 2], vals[:, 2], loss, 4)
     assert list(idx - 7_000_000_000) == [b0, b1, b2]
     assert list(val) == [cand[b0, 0], cand[b1, 1], cand[b2, 2]]
+    ctx.tpe_set_option(2, 1)  # the pruned path across the same chunk boundaries
+    idx2, val2, _ = ctx.tpe_score_select(cand, index_offset=7_000_000_000)
+    assert list(idx2) == list(idx) and list(val2) == list(val)
+    ctx.close()
 
 
 def test_edges_empty_history_empty_candidates_wide_space(ctx):
