@@ -375,6 +375,7 @@ def main():
         return
     # ---- roofline from the live per-kernel event times (this rank's slice; every rank does the same work)
     n_cont, n_quant = 20, 10
+    launch_rows = min(n_local, 1 << int(os.environ.get("KB_CHUNK_LOG2", "22")))  # candidates per kernel launch (staged chunk)
     ce_cont = float(n_local) * n_cont * (K_l + K_g) * args.steps
     ce_quant = float(n_local) * n_quant * (K_l + K_g) * args.steps
     names = ["tpe_stage_kernel", "tpe_score_cont_kernel", "tpe_score_quant_kernel", "tpe_rescore+pick"]
@@ -386,16 +387,19 @@ def main():
         if k == 1 and ms_k > 0:
             a = ce_cont / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
-                       frac=a / peaks["mufu_ex2_gops"], traffic=182.6e6,
-                       traffic_note="dram read+write bytes per launch (2^20-candidate chunk), ncu --set full, profiles/r01_ncu_tpe_score.md")
+                       frac=a / peaks["mufu_ex2_gops"], traffic=182.6e6 * launch_rows / float(1 << 20),
+                       traffic_note=f"dram read+write bytes per launch: 182.6 MB measured by ncu --set full on a 2^20-candidate launch "
+                                    f"(profiles/r01_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches "
+                                    "(the traffic is the candidate columns, read once)")
         if k == 2 and ms_k > 0:
             a = ce_quant / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G CDF-pair evals/s (2 exp = 2 MUFU.EX2 each, algorithmic)", achieved=a,
-                       peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2), traffic=198.6e6,
+                       peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2), traffic=195.6e6 * launch_rows / float(1 << 20),
                        note="frac > 1 is not an error: the peak is the SFU roofline of the erf formulation (2 exp per evaluation); "
                             "on-grid components x on-grid candidates take the look-up class (1 LDS + 1 FFMA per evaluation, "
                             "no SFU), which is bound by shared-memory load issue instead",
-                       traffic_note="dram read+write bytes per launch (2^20-candidate chunk), ncu --set full, profiles/r01_ncu_tpe_score.md")
+                       traffic_note=f"dram read+write bytes per launch: 195.6 MB measured by ncu --set full on a 2^20-candidate launch, "
+                                    f"scaled to this run's {launch_rows}-candidate launches")
         if k == 0 and ms_k > 0:
             bytes_alg = float(n_local) * D * 8 * args.steps + float(n_local) * (n_cont * 8 + n_quant * 16) * args.steps
             a = bytes_alg / (ms_k * 1e-3) / 1e9
