@@ -180,7 +180,13 @@ int kb_cmaes_create(kb_ctx *ctx, int n, const double *mean, double sigma, int po
  * row-major supplied by the caller (NULL: drawn on the device, Philox keyed by seed).  No
  * resampling; out-of-bounds coordinates are clipped when bounds exist (repairInfeasibleParams). */
 int kb_cmaes_ask(kb_ctx *ctx, int lam, const double *z, uint64_t seed, double *x);
-/* Optimizer.Tell(solutions): x[popsize x n] row-major, f[popsize] lower is better. */
+/* Optimizer.Tell(solutions): x[popsize x n] row-major, f[popsize] lower is better.
+ * With a communicator of W ranks (kb_comm_init) the population is sharded by rows: every rank creates the optimiser
+ * with the same (global) popsize, asks for its popsize / W rows (rank r owns rows [r, r+1) * popsize / W; device-drawn
+ * z continues one global Philox stream) and tells them with their popsize / W objective values.  The ranking is
+ * global (one all-gather of f), y_w and the rank-mu sum are all-reduced, everything else -- mean, sigma, paths, C and
+ * its eigensystem -- is replicated, so afterwards all ranks hold the same state (equal to the single-GPU state to
+ * rounding).  popsize must be a multiple of W. */
 int kb_cmaes_tell(kb_ctx *ctx, const double *x, const double *f);
 /* Any pointer may be NULL.  B[i*n+j] = component i of eigenvector j, D = sqrt(eigenvalues), both
  * canonical (ascending, largest-|component| positive); they refer to the current C. */

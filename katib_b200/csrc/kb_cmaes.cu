@@ -36,6 +36,7 @@ struct KbCma {
     double *d_X = nullptr, *d_Xt = nullptr, *d_Y = nullptr, *d_Yt = nullptr, *d_V = nullptr, *d_Z = nullptr;
     int *d_perm = nullptr, *d_flag = nullptr, *d_count = nullptr;
     void *d_eigws = nullptr;
+    double *d_fall = nullptr, *d_wrow = nullptr;  // sharded tell: all ranks' objective values; this rank's row weights
 };
 
 static void cma_free(KbCma *c) {
@@ -44,6 +45,7 @@ static void cma_free(KbCma *c) {
                       c->d_wio, c->d_yw, c->d_c2yw, c->d_lo, c->d_hi, c->d_scal, c->d_X, c->d_Xt, c->d_Y, c->d_Yt, c->d_V, c->d_Z};
     for (double *p : ptrs) cudaFree(p);
     cudaFree(c->d_perm); cudaFree(c->d_flag); cudaFree(c->d_count); cudaFree(c->d_eigws); cudaFree(c->d_Bt);
+    cudaFree(c->d_fall); cudaFree(c->d_wrow);
     delete c;
 }
 int kb_cmaes_free(kb_ctx *ctx) {
@@ -101,12 +103,13 @@ struct CmaPhilox {
     }
 };
 // z ~ N(0, I) for flagged rows: Philox keyed by seed, counter (generation, row, element, attempt)
-__global__ void cma_draw_z_kernel(int lam, int n, uint64_t seed, uint32_t gen, uint32_t attempt, const int *flag, double *Z) {
+__global__ void cma_draw_z_kernel(int lam, int n, uint64_t seed, uint32_t gen, uint32_t attempt, const int *flag, double *Z,
+                                  uint32_t row0) {
     const int k = blockIdx.x;
     if (flag && flag[k] == 0) return;
     CmaPhilox ph{(uint32_t)seed, (uint32_t)(seed >> 32)};
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const uint4 r = ph(gen, (uint32_t)k, (uint32_t)i, attempt);
+        const uint4 r = ph(gen, row0 + (uint32_t)k, (uint32_t)i, attempt);  // row0: first population row of this rank
         double u1 = (double)(((unsigned long long)r.x << 21) ^ (unsigned long long)(r.y >> 11)) * (1.0 / 9007199254740992.0);
         const double u2 = (double)(((unsigned long long)r.z << 21) ^ (unsigned long long)(r.w >> 11)) * (1.0 / 9007199254740992.0);
         u1 = u1 < 1e-300 ? 1e-300 : u1;
@@ -116,8 +119,21 @@ __global__ void cma_draw_z_kernel(int lam, int n, uint64_t seed, uint32_t gen, u
 // Y[k,:] = (X[perm[k],:] - mean) / sigma
 __global__ void cma_sorted_y_kernel(int lam, int n, const double *X, const int *perm, const double *mean, double sigma, double *Y) {
     const int k = blockIdx.x;
-    const int src = perm[k];
+    const int src = perm ? perm[k] : k;
     for (int i = threadIdx.x; i < n; i += blockDim.x) Y[(size_t)k * n + i] = (X[(size_t)src * n + i] - mean[i]) / sigma;
+}
+// population sharded over ranks: this rank's share of y_w, rows in caller order with their rank-based weights
+__global__ void cma_yw_rows_kernel(int rows, int n, const double *Y, const double *wrow, double *yw) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double acc = 0.0;
+    for (int k = 0; k < rows; k++) { const double w = wrow[k]; if (w > 0.0) acc += Y[(size_t)k * n + i] * w; }
+    yw[i] = acc;
+}
+// y += a * x
+__global__ void cma_axpy_kernel(size_t count, double *y, const double *x, double a) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) y[i] += a * x[i];
 }
 // yw[i] = sum_{k<mu} w_k Y[k,i]; mean += cm * sigma * yw
 __global__ void cma_yw_kernel(int mu, int n, const double *Y, const double *w, double *yw, double *mean, double cm_sigma) {
@@ -301,7 +317,10 @@ extern "C" int kb_cmaes_ask(kb_ctx *ctx, int lam, const double *z, uint64_t seed
         for (int attempt = 0; attempt <= CMA_MAX_RESAMPLE; attempt++) {
             const int last = attempt == CMA_MAX_RESAMPLE || !c->bounded;
             KB_CUDA(ctx, cudaMemsetAsync(c->d_count, 0, sizeof(int), s));
-            cma_draw_z_kernel<<<lam, 128, 0, s>>>(lam, n, seed, (uint32_t)c->g, (uint32_t)attempt, c->d_flag, c->d_Z);
+            int world = 1, rank = 0;
+            kb_comm_world(ctx, &world, &rank);  // sharded population: every rank draws its own rows of the global stream
+            cma_draw_z_kernel<<<lam, 128, 0, s>>>(lam, n, seed, (uint32_t)c->g, (uint32_t)attempt, c->d_flag, c->d_Z,
+                                                  (uint32_t)(world > 1 ? rank * lam : 0));
             KB_LAUNCH_CHECK(ctx);
             if ((rc = kb_dgemm_nt(ctx, lam, n, n, c->d_Z, n, c->d_D, c->d_B, n, c->d_Xt, n, c->sigma, 0.0, s))) return rc;
             cma_finish_x_kernel<<<lam, 128, 0, s>>>(lam, n, c->d_mean, c->d_lo, c->d_hi, c->d_Xt, c->d_X, c->d_flag, c->d_count, last);
@@ -318,6 +337,74 @@ extern "C" int kb_cmaes_ask(kb_ctx *ctx, int lam, const double *z, uint64_t seed
     return KB_OK;
 }
 
+// Population sharded by rows over the ranks of the communicator: state, eigensystem and every
+// n-sized update are replicated; a rank holds lam / world rows of X.  Exchanges per generation: one all-gather of the
+// lam objective values (the ranking is global), one all-reduce of the n-vector y_w and one of the n x n rank-mu partial.
+// Sums meet in a different order than on one GPU, so states agree to rounding (1e-13 relative), not bit for bit.
+static int cma_tell_sharded(kb_ctx *ctx, KbCma *c, const double *x, const double *f, int world, int rank, cudaStream_t s) {
+    const int n = c->n, lam = c->lam;
+    if (lam % world) return kb_fail(ctx, KB_ERR_UNSUPPORTED, "kb_cmaes_tell: popsize %d is not a multiple of the %d ranks", lam, world);
+    const int L = lam / world, r0 = rank * L;
+    if (!c->d_fall) { CMA_ALLOC(c->d_fall, lam); CMA_ALLOC(c->d_wrow, lam); }
+    int rc;
+    c->g += 1;
+    KB_CUDA(ctx, cudaMemcpyAsync(c->d_fall + r0, f, sizeof(double) * (size_t)L, cudaMemcpyHostToDevice, s));
+    if ((rc = kb_comm_allgather(ctx, c->d_fall + r0, c->d_fall, sizeof(double) * (size_t)L, s))) return rc;
+    std::vector<double> fall((size_t)lam);
+    KB_CUDA(ctx, cudaMemcpyAsync(fall.data(), c->d_fall, sizeof(double) * (size_t)lam, cudaMemcpyDeviceToHost, s));
+    KB_CUDA(ctx, cudaMemcpyAsync(c->d_X, x, sizeof(double) * (size_t)L * n, cudaMemcpyHostToDevice, s));
+    KB_CUDA(ctx, cudaStreamSynchronize(s));
+    std::vector<int> perm((size_t)lam);
+    std::iota(perm.begin(), perm.end(), 0);
+    std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return fall[(size_t)a] < fall[(size_t)b]; });
+    std::vector<double> wrow((size_t)L, 0.0);
+    for (int pos = 0; pos < lam; pos++) {
+        const int gidx = perm[(size_t)pos];
+        if (gidx >= r0 && gidx < r0 + L) wrow[(size_t)(gidx - r0)] = c->h_w[(size_t)pos];
+    }
+    KB_CUDA(ctx, cudaMemcpyAsync(c->d_wrow, wrow.data(), sizeof(double) * (size_t)L, cudaMemcpyHostToDevice, s));
+    cma_sorted_y_kernel<<<L, 128, 0, s>>>(L, n, c->d_X, nullptr, c->d_mean, c->sigma, c->d_Y);
+    KB_LAUNCH_CHECK(ctx);
+    cma_yw_rows_kernel<<<(n + 127) / 128, 128, 0, s>>>(L, n, c->d_Y, c->d_wrow, c->d_yw);
+    KB_LAUNCH_CHECK(ctx);
+    if ((rc = kb_comm_allreduce_sum_f64(ctx, c->d_yw, (size_t)n, s))) return rc;
+    cma_axpy_kernel<<<(n + 127) / 128, 128, 0, s>>>((size_t)n, c->d_mean, c->d_yw, c->cm * c->sigma);  // eq.41
+    KB_LAUNCH_CHECK(ctx);
+    if ((rc = kb_dgemm_nt(ctx, n, n, n, c->d_B, n, c->d_Dinv, c->d_B, n, c->d_C2, n, 1.0, 0.0, s))) return rc;
+    cma_gemv_kernel<<<(n * 32 + 255) / 256, 256, 0, s>>>(n, c->d_C2, c->d_yw, c->d_c2yw);
+    KB_LAUNCH_CHECK(ctx);
+    cma_psigma_kernel<<<1, 256, 0, s>>>(n, c->d_ps, c->d_c2yw, c->c_sigma, sqrt(c->c_sigma * (2.0 - c->c_sigma) * c->mu_eff), c->d_scal);
+    KB_LAUNCH_CHECK(ctx);
+    double norm2 = 0.0;
+    KB_CUDA(ctx, cudaMemcpyAsync(&norm2, c->d_scal, sizeof(double), cudaMemcpyDeviceToHost, s));
+    if ((rc = kb_dgemm_nt(ctx, L, n, n, c->d_Y, n, nullptr, c->d_C2, n, c->d_V, n, 1.0, 0.0, s))) return rc;
+    cma_wio_kernel<<<(L * 32 + 255) / 256, 256, 0, s>>>(L, n, c->d_V, c->d_wrow, c->d_wio);  // eq.46
+    KB_LAUNCH_CHECK(ctx);
+    if ((rc = kb_transpose(ctx, L, n, c->d_Y, c->d_Yt, s))) return rc;
+    KB_CUDA(ctx, cudaStreamSynchronize(s));
+    const double norm_ps = sqrt(norm2);
+    c->sigma *= exp((c->c_sigma / c->d_sigma) * (norm_ps / c->chi_n - 1.0));
+    if (c->sigma > CMA_SIGMA_MAX) c->sigma = CMA_SIGMA_MAX;
+    const double hl = norm_ps / sqrt(1.0 - pow(1.0 - c->c_sigma, 2.0 * (double)(c->g + 1)));
+    const double hr = (1.4 + 2.0 / ((double)n + 1.0)) * c->chi_n;
+    const double h_sigma = hl < hr ? 1.0 : 0.0;
+    cma_pc_kernel<<<(n + 127) / 128, 128, 0, s>>>(n, c->d_pc, c->d_yw, c->cc, h_sigma * sqrt(c->cc * (2.0 - c->cc) * c->mu_eff));  // eq.45
+    KB_LAUNCH_CHECK(ctx);
+    const double delta_h = (1.0 - h_sigma) * c->cc * (2.0 - c->cc);
+    const double keep = 1.0 + c->c1 * delta_h - c->c1 - c->cmu * c->sum_w;
+    const size_t nn = (size_t)n * n;
+    cma_rank_one_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, s>>>(n, c->d_C, c->d_pc, keep, c->c1);  // eq.47
+    KB_LAUNCH_CHECK(ctx);
+    // this rank's share of sum_k w_k^o y_k y_k^T (C^-1/2 is no longer needed: its buffer takes the partial)
+    if ((rc = kb_dgemm_nt(ctx, n, n, L, c->d_Yt, L, c->d_wio, c->d_Yt, L, c->d_C2, n, 1.0, 0.0, s))) return rc;
+    if ((rc = kb_comm_allreduce_sum_f64(ctx, c->d_C2, nn, s))) return rc;
+    cma_axpy_kernel<<<(unsigned)((nn + 255) / 256), 256, 0, s>>>(nn, c->d_C, c->d_C2, c->cmu);
+    KB_LAUNCH_CHECK(ctx);
+    c->have_eig = false;
+    KB_CUDA(ctx, cudaStreamSynchronize(s));
+    return KB_OK;
+}
+
 extern "C" int kb_cmaes_tell(kb_ctx *ctx, const double *x, const double *f) {
     if (!ctx) return KB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -330,6 +417,11 @@ extern "C" int kb_cmaes_tell(kb_ctx *ctx, const double *x, const double *f) {
     int rc = cma_ensure_eig(ctx, c, s);  // Tell uses the factors of the C the population was drawn from
     if (rc) return rc;
     KbProf pf(ctx, 8, s);
+    {
+        int world = 1, rank = 0;
+        kb_comm_world(ctx, &world, &rank);
+        if (world > 1) return cma_tell_sharded(ctx, c, x, f, world, rank, s);  // x, f: this rank's lam / world rows
+    }
     c->g += 1;
     std::vector<int> perm((size_t)lam);
     std::iota(perm.begin(), perm.end(), 0);

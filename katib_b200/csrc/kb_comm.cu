@@ -11,6 +11,8 @@ typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;  // 0 = ncclSuccess
 typedef int ncclDataType_t;
 #define KB_NCCL_INT8 0
+#define KB_NCCL_FLOAT64 8
+#define KB_NCCL_SUM 0
 
 struct KbNccl {
     void *handle = nullptr;
@@ -18,6 +20,7 @@ struct KbNccl {
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
     std::string why;
 };
@@ -33,6 +36,7 @@ static KbNccl *nccl_api() {
         api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.handle, "ncclCommInitRank");
         api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");
         api.AllGather = (decltype(api.AllGather))dlsym(api.handle, "ncclAllGather");
+        api.AllReduce = (decltype(api.AllReduce))dlsym(api.handle, "ncclAllReduce");
         api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.handle, "ncclGetErrorString");
         if (!api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.AllGather) {
             api.why = "libnccl is missing a required symbol";
@@ -99,6 +103,16 @@ int kb_comm_allgather(kb_ctx *ctx, const void *send, void *recv, size_t bytes, c
     if (!ctx->comm || !ctx->comm->comm) return kb_fail(ctx, KB_ERR_COMM, "kb_comm_allgather: no communicator");
     ncclResult_t r = nccl_api()->AllGather(send, recv, bytes, KB_NCCL_INT8, ctx->comm->comm, s);
     if (r) return kb_fail(ctx, KB_ERR_COMM, "ncclAllGather: %s", nccl_api()->GetErrorString ? nccl_api()->GetErrorString(r) : "?");
+    ctx->launches++;
+    return KB_OK;
+}
+
+// in-place sum of `count` doubles over the ranks (the CMA-ES rank-mu partials, kb_cmaes.cu)
+int kb_comm_allreduce_sum_f64(kb_ctx *ctx, double *buf, size_t count, cudaStream_t s) {
+    if (!ctx->comm || !ctx->comm->comm) return kb_fail(ctx, KB_ERR_COMM, "kb_comm_allreduce_sum_f64: no communicator");
+    if (!nccl_api()->AllReduce) return kb_fail(ctx, KB_ERR_COMM, "kb_comm_allreduce_sum_f64: libnccl has no ncclAllReduce");
+    ncclResult_t r = nccl_api()->AllReduce(buf, buf, count, KB_NCCL_FLOAT64, KB_NCCL_SUM, ctx->comm->comm, s);
+    if (r) return kb_fail(ctx, KB_ERR_COMM, "ncclAllReduce: %s", nccl_api()->GetErrorString ? nccl_api()->GetErrorString(r) : "?");
     ctx->launches++;
     return KB_OK;
 }

@@ -208,6 +208,7 @@ int kb_sobol_free(kb_ctx *ctx);
 int kb_cmaes_free(kb_ctx *ctx);
 int kb_comm_free(kb_ctx *ctx);
 int kb_comm_allgather(kb_ctx *ctx, const void *send, void *recv, size_t bytes, cudaStream_t s);
+int kb_comm_allreduce_sum_f64(kb_ctx *ctx, double *buf, size_t count, cudaStream_t s);
 
 // ---- device helpers ------------------------------------------------------------------------------------
 #ifdef __CUDACC__

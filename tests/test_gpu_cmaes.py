@@ -169,3 +169,18 @@ def test_errors(ctx):
     with pytest.raises(kb.KbError):
         c2.cmaes_create(np.zeros(3), -1.0)
     c2.close()
+
+
+def test_sharded_population_tracks_single_gpu():
+    """SURVEY.md 8(e), CMA-ES row: population sharded by rows over NCCL ranks (one all-gather of f, all-reduces of y_w
+    and the rank-mu partial).  Needs two GPUs; the single-GPU CI box skips it (run it with `gpurun --gpus 2`)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(here, "mp_cmaes_sharded.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0 and "SHARDED OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
