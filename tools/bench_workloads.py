@@ -242,6 +242,28 @@ def tpe3(args):
         t2 = time.perf_counter()
         if i >= 20:
             lat_full.append(t2 - t0); lat_suggest.append(t2 - t1)
+    # the same shape through the wire-level boundary: kb_service_get_suggestions on serialized api.proto messages, a
+    # closed loop in which every request carries ALL trials so far (as the controller sends them) and one of them is new
+    import _pb
+    svc = kb.Service(0)
+    space = [_pb.parameter("lr", "DOUBLE", max="0.03", min="0.01"), _pb.parameter("num-layers", "INT", max="5", min="2"),
+             _pb.parameter("optimizer", "CATEGORICAL", list=["sgd", "adam", "ftrl"])]
+    exp = _pb.experiment("hp", "tpe", [("random_state", "10")], "MINIMIZE", "loss", space)
+    trials, lat_svc, pending = [], [], None
+    for i in range(320):
+        if pending is not None:
+            d = dict(pending)
+            fval = (float(d["lr"]) - 0.02) ** 2 * 1e4 + 0.1 * int(d["num-layers"]) + (d["optimizer"] != "adam")
+            trials.append(_pb.trial(f"t{i}", pending, "SUCCEEDED", [("loss", repr(fval))]))
+        req = _pb.get_suggestions_request(exp, trials, 1, i + 1)
+        t0 = time.perf_counter()
+        code, reply, msg = svc.get_suggestions(req)
+        dt = time.perf_counter() - t0
+        assert code == 0, msg
+        pending = _pb.parse_reply(reply)[0]
+        if len(trials) >= 100:
+            lat_svc.append(dt)
+    svc.close()
     cand = ctx.tpe_sample_candidates(24, seed=10)
     t0 = time.perf_counter()
     reps = 200
@@ -257,6 +279,10 @@ def tpe3(args):
         "dtype": "f32/f64", "data": "synthetic",
         "config": {"workload": "TPE on the hp-tuning (lr, num-layers, optimizer) space, 100-trial history, 24 candidates", "baseline_config": "configs[0]"},
         "p95_ms": p(lat_full, 95), "suggest_only_p50_ms": p(lat_suggest, 50), "suggest_only_p95_ms": p(lat_suggest, 95),
+        "service_p50_ms": p(lat_svc, 50), "service_p95_ms": p(lat_svc, 95),
+        "service_note": "kb_service_get_suggestions on serialized GetSuggestionsRequest bytes, 100..320 trials resent in full every "
+                        "call, one new Succeeded trial per call: protobuf parse + trial conversion + matching + history append + "
+                        "Parzen build + suggest + reply encoding",
         "e2e": {"value": p(lat_full, 50), "unit": "ms", "h2d_bytes_per_step": n * 4 * 8, "d2h_bytes_per_step": 72},
         "gpu_launches": ctx.launch_count(), "roofline": None,
         "cpu_baseline": {"value": cpu * 1e3, "unit": "ms per suggestion (score+select only)", "cores": 1, "kind": "port",
