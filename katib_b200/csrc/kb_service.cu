@@ -365,6 +365,10 @@ static const Param *find_param(const std::vector<Param> &space, const std::strin
 static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &metric, const std::vector<Param> &space,
                           std::vector<ConvertedTrial> &out, std::string &err) {
     out.clear();
+    out.reserve(in.size());
+    std::map<std::string, size_t> by_name;  // position in `out`
+    std::map<std::string, const Param *> param_of;  // first entry of a name wins, as in find_param
+    for (const Param &p : space) param_of.emplace(p.name, &p);
     for (const TrialMsg &kt : in) {
         ConvertedTrial t; t.name = kt.name;
         if (!kt.start_time.empty() && !rfc3339_ok(kt.start_time)) { err = "parsing time \"" + kt.start_time + "\" as \"2006-01-02T15:04:05.999999999Z07:00\": cannot parse"; return false; }
@@ -387,8 +391,9 @@ static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &me
             if (!found) { err = "No objective metric in Trial " + kt.name; return false; }
         }
         for (const KV &a : kt.assignments) {
-            const Param *p = find_param(space, a.name);
-            if (!p) continue;  // a name outside the search space matches no case of the Go type switch
+            const auto pit = param_of.find(a.name);
+            if (pit == param_of.end()) continue;  // a name outside the search space matches no case of the Go type switch
+            const Param *p = pit->second;
             double v = 0;
             if (p->kind == KB_UNIFORM || p->kind == KB_DISCRETE) { if (!go_parse_float(a.value, v, err)) return false; }
             else if (p->kind == KB_INT || p->kind == KB_STEP_INT) {
@@ -404,9 +409,9 @@ static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &me
             t.params[a.name] = v;
         }
         // a Go map keyed by trial name: a later duplicate replaces the earlier entry
-        bool replaced = false;
-        for (ConvertedTrial &o : out) if (o.name == t.name) { o = t; replaced = true; }
-        if (!replaced) out.push_back(t);
+        auto seen = by_name.find(t.name);
+        if (seen != by_name.end()) out[seen->second] = t;
+        else { by_name.emplace(t.name, out.size()); out.push_back(t); }
     }
     return true;
 }
