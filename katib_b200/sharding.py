@@ -29,3 +29,14 @@ def merge_winners(scores, indices, values):
             if better:
                 out_s[d], out_i[d], out_v[d] = scores[r, d], indices[r, d], values[r, d]
     return out_s, out_i, out_v
+
+
+def population_row_weights(f_all, weights, begin, end):
+    """CMA-ES with the population sharded by rows (cma_tell_sharded in kb_cmaes.cu): the recombination weight of each of
+    this rank's rows [begin, end).  The ranking is global -- ascending objective value, ties by global row index (a stable
+    sort, as Optimizer.Tell sorts its solutions) -- and weights[p] belongs to the row ranked p."""
+    f_all = np.asarray(f_all, float)
+    order = np.argsort(f_all, kind="stable")
+    w = np.empty(len(f_all))
+    w[order] = np.asarray(weights, float)
+    return w[begin:end]

@@ -81,3 +81,53 @@ def test_two_rank_merge_equals_unsharded_oracle():
 def test_merge_rule_ties_and_empty_ranks():
     s, i, v = merge_winners([[1.0, 2.0], [1.0, 3.0], [0.0, 0.0]], [[7, 5], [4, 9], [-1, -1]], [[.1, .2], [.3, .4], [0, 0]])
     assert list(i) == [4, 9] and list(v) == [.3, .4] and list(s) == [1.0, 3.0]
+
+
+def _cma_problem():
+    rng = np.random.Generator(np.random.PCG64(5))
+    lam, n = 24, 7
+    Y = rng.normal(size=(lam, n))
+    f = np.sum(Y ** 2, axis=1)
+    f[5] = f[20]  # a tie across the shard boundary: the global row index decides
+    wts = np.log((lam + 1) / 2) - np.log(np.arange(1, lam + 1))  # positive for the better half, negative after
+    return Y, f, wts
+
+
+def _cma_worker(rank, world, port, q):
+    from katib_b200.sharding import population_row_weights
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    Y, f, wts = _cma_problem()
+    lo, hi = shard_range(len(f), world, rank)
+    mine = torch.tensor(f[lo:hi])
+    gathered = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(gathered, mine)                      # the ranking needs every objective value
+    w = population_row_weights(torch.cat(gathered).numpy(), wts, lo, hi)
+    yw = torch.tensor((np.maximum(w, 0.0)[:, None] * Y[lo:hi]).sum(axis=0))
+    P = torch.tensor((Y[lo:hi].T * w) @ Y[lo:hi])       # this rank's share of sum_k w_k y_k y_k^T
+    dist.all_reduce(yw)
+    dist.all_reduce(P)
+    if rank == 0:
+        q.put((w.tolist(), yw.numpy().tolist(), P.numpy().tolist()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_cmaes_partials_equal_the_unsharded_sums():
+    """Host-side rule of the sharded CMA-ES tell: global stable ranking -> per-row weights; the all-reduced y_w and
+    rank-mu partials equal the single-process sums."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cma_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    w0, yw, P = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    Y, f, wts = _cma_problem()
+    order = sorted(range(len(f)), key=lambda k: (f[k], k))
+    w = np.empty(len(f)); w[order] = wts
+    assert w[5] > w[20]                                   # the tie went to the lower global index
+    np.testing.assert_array_equal(w0, w[:12])
+    np.testing.assert_allclose(yw, (np.maximum(w, 0)[:, None] * Y).sum(axis=0), rtol=1e-14, atol=1e-15)
+    np.testing.assert_allclose(P, (Y.T * w) @ Y, rtol=1e-13, atol=1e-14)
