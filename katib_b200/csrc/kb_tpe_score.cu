@@ -1226,11 +1226,15 @@ static int tpe_precheck(kb_ctx *ctx, int64_t n_cand, const void *cand, const cha
 static int tpe_run_host(kb_ctx *ctx, int64_t n_cand, const double *cand, int64_t index_offset, bool select, double *scores_host) {
     const int D = ctx->D;
     cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
-    const int64_t rows = n_cand < KB_CHUNK_ROWS ? (n_cand > 0 ? n_cand : 1) : KB_CHUNK_ROWS;
+    // chunk size of the host path: at least eight chunks when the set allows it, so that the copy of chunk k + 1
+    // hides behind the kernels of chunk k (two chunks would leave half of the H2D time exposed), in 64 Ki-row steps
+    int64_t rows = (((n_cand + 7) / 8 + 65535) / 65536) * 65536;
+    rows = std::min<int64_t>(std::max<int64_t>(rows, 1 << 18), KB_CHUNK_ROWS);
+    if (rows > n_cand) rows = n_cand > 0 ? n_cand : 1;
     int rc = tpe_ensure_scratch(ctx, rows, n_cand, true, scores_host != nullptr);
     if (rc) return rc;
     if (select && (rc = tpe_reset_selection(ctx, s))) return rc;
-    const int64_t cap = ctx->chunk_cap;
+    const int64_t cap = std::min<int64_t>(ctx->chunk_cap, rows);
     int buf = 0;
     for (int64_t off = 0; off < n_cand; off += cap, buf ^= 1) {
         const int n = (int)(n_cand - off < cap ? n_cand - off : cap);
