@@ -413,6 +413,16 @@ def main():
                 "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel on this GPU in this run (of measured); "
                                "MEASURED_PEAKS.json has HBM and bf16 only",
                 "kernels": kern, "measured_peaks": peaks}
+    # BASELINE.json's metric names two figures: candidates/s (above) and the GetSuggestions p50 latency, which is quoted on
+    # configs[0] (3 parameters, 100 trials, 24 candidates) -- measured here on rank 0's GPU, a few hundred calls
+    latency = None
+    if os.environ.get("KB_BENCH_LATENCY", "1") == "1":
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_workloads
+        lt = bench_workloads.tpe3(args, calls=300, device=local_rank, emit=False)
+        latency = {k: lt[k] for k in ("metric", "value", "unit", "p95_ms", "suggest_only_p50_ms", "service_p50_ms", "service_p95_ms")}
+        latency["config"] = lt["config"]
+        latency["cpu_baseline_ms"] = lt["cpu_baseline"]["value"]
     cores = 1
     n_sample = args.cpu_sample or 384
     cpu_v, cpu_dt = cpu_baseline(kinds, lows, highs, steps, nch, vals, loss, n_sample, cores)
@@ -424,7 +434,7 @@ def main():
            "cpu_baseline": {"value": cpu_v, "unit": "candidates/s", "cores": cores, "kind": "port",
                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
-           "merged_duplicates": merged, "pruned": pruned,
+           "merged_duplicates": merged, "pruned": pruned, "latency": latency,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
     print(json.dumps(out), flush=True)
     shutdown()

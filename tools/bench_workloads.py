@@ -221,18 +221,18 @@ def cmaes(args):
 
 
 # ------------------------------------------------------------------------------------------------ configs[0]
-def tpe3(args):
-    """GetSuggestions latency shape: 3 parameters (double, int, categorical), 100-trial history, 24 EI candidates."""
+def tpe3(args, calls=1000, device=0, emit=True):
+    """GetSuggestions latency shape: 3 parameters (double, int, categorical), 100-trial history, 24 EI candidates.
+    Also called by the headline bench (emit=False) for its `latency` object."""
     import katib_b200 as kb
     import _oracle as O
-    ctx = kb.Context(0)
+    ctx = kb.Context(device)
     rng = np.random.Generator(np.random.PCG64(1))
     kind = [kb.KB_UNIFORM, kb.KB_INT, kb.KB_CATEGORICAL]
     ctx.space_set(kind, [0.01, 2, 0], [0.03, 5, 0], n_choices=[0, 0, 3])
     n = 100
     vals = np.stack([rng.uniform(0.01, 0.03, n), np.floor(rng.uniform(2, 6, n)), np.floor(rng.uniform(0, 3, n))], axis=1)
     loss = (vals[:, 0] - 0.02) ** 2 * 1e4 + 0.1 * vals[:, 1] + (vals[:, 2] != 1) + rng.normal(0, 0.01, n)
-    calls = 1000
     lat_full, lat_suggest = [], []
     for i in range(calls + 20):
         t0 = time.perf_counter()
@@ -245,7 +245,7 @@ def tpe3(args):
     # the same shape through the wire-level boundary: kb_service_get_suggestions on serialized api.proto messages, a
     # closed loop in which every request carries ALL trials so far (as the controller sends them) and one of them is new
     import _pb
-    svc = kb.Service(0)
+    svc = kb.Service(device)
     space = [_pb.parameter("lr", "DOUBLE", max="0.03", min="0.01"), _pb.parameter("num-layers", "INT", max="5", min="2"),
              _pb.parameter("optimizer", "CATEGORICAL", list=["sgd", "adam", "ftrl"])]
     exp = _pb.experiment("hp", "tpe", [("random_state", "10")], "MINIMIZE", "loss", space)
@@ -273,7 +273,7 @@ def tpe3(args):
         O.tpe_score_categorical(cand[:, 2], vals[:, 2], loss, 3)
     cpu = (time.perf_counter() - t0) / reps
     p = lambda a, q: float(np.percentile(np.asarray(a) * 1e3, q))
-    print(json.dumps({
+    out = {
         "metric": "getsuggestions_latency_ms_p50", "value": p(lat_full, 50), "unit": "ms (history upload + Parzen build + sample + score + select)",
         "n_gpus": 1, "steps": calls, "warmup": 20, "ms_per_step": p(lat_full, 50), "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32/f64", "data": "synthetic",
@@ -286,8 +286,11 @@ def tpe3(args):
         "e2e": {"value": p(lat_full, 50), "unit": "ms", "h2d_bytes_per_step": n * 4 * 8, "d2h_bytes_per_step": 72},
         "gpu_launches": ctx.launch_count(), "roofline": None,
         "cpu_baseline": {"value": cpu * 1e3, "unit": "ms per suggestion (score+select only)", "cores": 1, "kind": "port",
-                         "sample": f"{reps} repetitions, oracle/tpe.c"}}))
+                         "sample": f"{reps} repetitions, oracle/tpe.c"}}
     ctx.close()
+    if emit:
+        print(json.dumps(out))
+    return out
 
 
 WORKLOADS = {"sobol": sobol, "tpe20": tpe20, "cmaes": cmaes, "tpe3": tpe3}
