@@ -228,7 +228,8 @@ int kb_service_validate_algorithm_settings(kb_service *svc, const void *request,
 const char *kb_service_last_message(const kb_service *svc);
 /* Introspection for tests: 0 CMA-ES population size in use, 1 restarts so far (IPOP / BIPOP), 2 internal trials,
  * 3 generation tag, 4 Complete observations, 5 history rows sent to the GPU so far (kb_tpe_set_history +
- * kb_tpe_append_history), 6 trials adopted under KB_SVC_ADOPT_UNKNOWN_TRIALS. */
+ * kb_tpe_append_history), 6 trials adopted under KB_SVC_ADOPT_UNKNOWN_TRIALS, 7 resent Trial messages recognised by
+ * their bytes as already synced into a finished state and therefore not parsed again. */
 long long kb_service_stat(kb_service *svc, int which);
 /* KB_SVC_ADOPT_UNKNOWN_TRIALS (default 0): a trial whose parameters match no trial this service suggested fails
  * GetSuggestions with "Same parameter is not found for Trial: <name>" in the reference (sample.go:126) -- which is

@@ -21,6 +21,7 @@
 #include <cstdlib>
 #include <map>
 #include <set>
+#include <unordered_set>
 
 #include "kb_internal.cuh"
 
@@ -87,6 +88,7 @@ struct ExperimentMsg {
 };
 struct TrialMsg {
     std::string name, start_time, completion_time;
+    uint64_t digest = 0;  // of the serialized message (see digest_bytes)
     int condition = 0;
     std::vector<KV> assignments, metrics;
 };
@@ -169,12 +171,35 @@ static TrialMsg parse_trial(PbReader r) {
     }
     return t;
 }
-static bool parse_request(const void *data, size_t n, GetSuggestionsRequestMsg &req) {
+// 64-bit digest of a serialized Trial.  The controller resends EVERY trial with every request
+// (suggestionclient.go:111-116); once a trial has reached a finished state here it is never updated again
+// (service.go:134-137 pushes value and state once), so a message whose bytes were already seen in that state needs
+// neither parsing nor conversion: same bytes, same (already validated) result, and nothing left to do with it.
+static uint64_t digest_bytes(const uint8_t *p, size_t n) {
+    uint64_t h = 0x9E3779B97F4A7C15ull ^ ((uint64_t)n * 0xFF51AFD7ED558CCDull);
+    while (n >= 8) {
+        uint64_t v; memcpy(&v, p, 8);
+        h = (h ^ v) * 0xFF51AFD7ED558CCDull; h ^= h >> 32;
+        p += 8; n -= 8;
+    }
+    uint64_t v = 0; memcpy(&v, p, n);
+    h = (h ^ v) * 0xC4CEB9FE1A85EC53ull; h ^= h >> 29;
+    h *= 0xFF51AFD7ED558CCDull; h ^= h >> 32;
+    return h;
+}
+
+static bool parse_request(const void *data, size_t n, GetSuggestionsRequestMsg &req,
+                          const std::unordered_set<uint64_t> *settled = nullptr, long long *skipped = nullptr) {
     PbReader r(data, n); int wt; PbReader sub(nullptr, 0); uint64_t v;
     while (!r.done()) {
         int f = r.next(wt, &sub, &v);
         if (f == 1 && wt == 2) req.experiment = parse_experiment(sub);
-        else if (f == 2 && wt == 2) req.trials.push_back(parse_trial(sub));
+        else if (f == 2 && wt == 2) {
+            const uint64_t dg = digest_bytes(sub.p, (size_t)(sub.end - sub.p));
+            if (settled && settled->count(dg)) { if (skipped) ++*skipped; continue; }
+            req.trials.push_back(parse_trial(sub));
+            req.trials.back().digest = dg;
+        }
         else if (f == 4 && wt == 0) req.current_request_number = (int)(int32_t)v;
         else if (f == 5 && wt == 0) req.total_request_number = (int)(int32_t)v;
     }
@@ -247,7 +272,7 @@ struct InternalTrial {
     int cma_generation = -1;
     bool cma_told = false;
 };
-struct ConvertedTrial { std::string name; int state = ST_RUNNING; double value = 0; std::map<std::string, double> params; };
+struct ConvertedTrial { std::string name; int state = ST_RUNNING; double value = 0; std::map<std::string, double> params; uint64_t digest = 0; };
 
 struct Status { int code = GRPC_OK; std::string msg; };
 static Status fail(int code, const std::string &m) { Status s; s.code = code; s.msg = m; return s; }
@@ -266,7 +291,8 @@ struct kb_service {
     // SyncTrials, i.e. after it was claimed, so every entry here is Running: the newest match is back().
     std::map<std::map<std::string, double>, std::vector<int>> unclaimed;
     std::vector<int> uploaded;  // trial ids whose rows are on the device as the TPE history, in row order
-    long long rows_uploaded = 0, adopted = 0;
+    long long rows_uploaded = 0, adopted = 0, skipped = 0;
+    std::unordered_set<uint64_t> settled;  // digests of Trial messages already synced into a finished state
     bool adopt_unknown = false;  // KB_SVC_ADOPT_UNKNOWN_TRIALS
     bool history_dirty = true;
     uint64_t draw_counter = 0;
@@ -370,7 +396,7 @@ static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &me
     std::map<std::string, const Param *> param_of;  // first entry of a name wins, as in find_param
     for (const Param &p : space) param_of.emplace(p.name, &p);
     for (const TrialMsg &kt : in) {
-        ConvertedTrial t; t.name = kt.name;
+        ConvertedTrial t; t.name = kt.name; t.digest = kt.digest;
         if (!kt.start_time.empty() && !rfc3339_ok(kt.start_time)) { err = "parsing time \"" + kt.start_time + "\" as \"2006-01-02T15:04:05.999999999Z07:00\": cannot parse"; return false; }
         if (!kt.completion_time.empty() && !rfc3339_ok(kt.completion_time)) { err = "parsing time \"" + kt.completion_time + "\" as \"2006-01-02T15:04:05.999999999Z07:00\": cannot parse"; return false; }
         switch (kt.condition) {
@@ -448,11 +474,12 @@ static Status SyncTrials(kb_service *s, const std::vector<ConvertedTrial> &kts) 
             s->mapping[kt.name] = id;
         } else id = it->second;
         InternalTrial &t = s->trials[(size_t)id];
-        if (finished(t.state)) continue;          // finished trials are never updated
+        if (finished(t.state)) { s->settled.insert(kt.digest); continue; }  // finished trials are never updated
         if (kt.state == t.state) continue;
         if (kt.state == ST_COMPLETE) t.value = kt.value;
         t.state = kt.state;
         s->history_dirty = true;
+        if (finished(t.state)) s->settled.insert(kt.digest);  // these bytes need no second look (see digest_bytes)
     }
     return Status();
 }
@@ -760,7 +787,7 @@ extern "C" int kb_service_get_suggestions(kb_service *s, const void *request, si
     std::lock_guard<std::mutex> lk(s->mu);
     GetSuggestionsRequestMsg req;
     Status st;
-    if (!parse_request(request, request_len, req)) st = fail(GRPC_INTERNAL, "malformed GetSuggestionsRequest");
+    if (!parse_request(request, request_len, req, &s->settled, &s->skipped)) st = fail(GRPC_INTERNAL, "malformed GetSuggestionsRequest");
     else st = GetSuggestions(s, req, s->reply);
     s->last_message = st.msg;
     if (st.code) s->reply.clear();
@@ -796,6 +823,7 @@ extern "C" long long kb_service_stat(kb_service *s, int which) {
         case 4: { long long c = 0; for (const InternalTrial &t : s->trials) c += t.state == ST_COMPLETE; return c; }
         case 5: return s->rows_uploaded;
         case 6: return s->adopted;
+        case 7: return s->skipped;
         default: return -1;
     }
 }

@@ -132,3 +132,27 @@ def test_cold_sync_of_thousands_of_trials_is_not_quadratic():
     assert dt < 2.0, dt  # parse + convert + match 4000 trials; the quadratic scan took ~16 M map comparisons
     print(f"cold sync of {n} trials: {dt * 1e3:.1f} ms")
     svc.close()
+
+
+def test_settled_trials_are_recognised_by_their_bytes():
+    """Every request resends every trial; a Trial message already synced into a finished state is skipped by digest.
+    A finished trial resent with DIFFERENT bytes is parsed again -- and, as in the reference, changes nothing."""
+    svc = kb.Service(0)
+    e, done = run_loop(svc, "tpe", 20)
+    assert svc.stat(7) > 10 * len(done) // 4          # most of what was resent over 20 requests was skipped
+    before_obs, before_skipped = svc.stat(4), svc.stat(7)
+    code, reply, msg = svc.get_suggestions(_pb.get_suggestions_request(e, done, 0, 0))
+    assert code == OK and svc.stat(7) == before_skipped + len(done)
+    # the same trial names, now claiming to have failed and carrying another loss: parsed, but finished trials stay as they are
+    changed = []
+    for r in range(18):
+        for i in range(2):
+            changed.append(_pb.trial(f"t{r}-{i}", [("x", "0.5"), ("k", "3"), ("c", "a")], "FAILED", [("loss", "123.0")]))
+    code, reply, msg = svc.get_suggestions(_pb.get_suggestions_request(e, changed, 1, 0))
+    assert code == OK, msg
+    assert svc.stat(7) == before_skipped + len(done) and svc.stat(4) == before_obs
+    # a malformed value in a message never seen before still fails the whole request, as toGoptunaTrials does
+    bad = _pb.trial("t0-0", [("x", "zero point five"), ("k", "3"), ("c", "a")], "SUCCEEDED", [("loss", "1.0")])
+    code, reply, msg = svc.get_suggestions(_pb.get_suggestions_request(e, done + [bad], 1, 0))
+    assert code == INTERNAL
+    svc.close()
