@@ -142,6 +142,7 @@ struct kb_ctx {
     KbWinner *d_win_all = nullptr;   // [world][D] (gather target)
     float *d_tie_score = nullptr;    // [n_numeric][tie_slots] FP32 score stored with each near-tie entry
     unsigned int tie_slots = 0;      // slots per numeric parameter in d_tie (power of two, sized from n_cand)
+    unsigned int tie_slots_floor = 0;  // lower bound on tie_slots, raised after an overflow
     void *d_tie_list = nullptr;      // [n_numeric][tie_slots] KbCand: compacted near ties awaiting FP64 re-scoring
     unsigned int *d_tie_count = nullptr;  // [n_numeric]
     int *d_slot_of_dim = nullptr;    // [D] index of a parameter inside its cont / quant / cat list

@@ -937,6 +937,10 @@ tpe_pick_kernel(const KbDim *__restrict__ dims, const KbSelect *__restrict__ sel
             v = v + dm.shift;
             v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         }
+        // sampleStepInt rounds to multiples of the step on [low - step/2, high + step/2] WITHOUT the shift: when
+        // high - low is not a multiple of the step the rounded value can pass `high` (or `low`); it is clamped here so
+        // that a suggestion never leaves the declared range (a superset of the restated goptuna rule)
+        if (dm.kind == KB_STEP_INT) v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         w.value = v;
         win[d] = w;
     }
@@ -1005,6 +1009,10 @@ tpe_suggest_small_kernel(const KbDim *__restrict__ dims, int n, uint64_t seed, K
             v = v + dm.shift;
             v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         }
+        // sampleStepInt rounds to multiples of the step on [low - step/2, high + step/2] WITHOUT the shift: when
+        // high - low is not a multiple of the step the rounded value can pass `high` (or `low`); it is clamped here so
+        // that a suggestion never leaves the declared range (a superset of the restated goptuna rule)
+        if (dm.kind == KB_STEP_INT) v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         if (dm.kind == KB_CATEGORICAL) {
             int c = (int)v;
             v = (double)(c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c));
@@ -1082,6 +1090,7 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
     {   // near-tie table: one slot per 32 candidates, within [2^12, 2^20] per numeric parameter
         unsigned int want = KB_TIE_SLOTS_MIN;
         while (want < KB_TIE_SLOTS_MAX && (int64_t)want * 32 < n_cand) want <<= 1;
+        if (want < ctx->tie_slots_floor) want = ctx->tie_slots_floor;  // raised after an overflow (tpe_retry_overflow)
         if (want > ctx->tie_slots) {
             const size_t nn = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
             cudaFree(ctx->d_tie); cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list);
@@ -1268,6 +1277,20 @@ extern "C" int kb_tpe_scores(kb_ctx *ctx, int64_t n_cand, const double *cand, do
     return KB_OK;
 }
 
+// The near-tie table is sized for the usual case (a handful of distinct values near the maximum).  A flat score
+// landscape -- e.g. a history so small that both mixtures are the prior alone -- puts every distinct candidate value
+// within the margin; then the pass is repeated with a table 16 times larger (twice at most, up to 2^20 slots per
+// parameter) before KB_ERR_OVERFLOW is reported.  Single rank only: a retry would unbalance the collective.
+static bool tpe_retry_overflow(kb_ctx *ctx, int rc, int attempt) {
+    if (rc != KB_ERR_OVERFLOW || attempt >= 2 || ctx->tie_slots >= KB_TIE_SLOTS_MAX) return false;
+    int world = 1, rank = 0;
+    kb_comm_world(ctx, &world, &rank);
+    if (world > 1) return false;
+    const unsigned long long next = (unsigned long long)ctx->tie_slots * 16ull;
+    ctx->tie_slots_floor = next > KB_TIE_SLOTS_MAX ? KB_TIE_SLOTS_MAX : (unsigned int)next;
+    return true;
+}
+
 extern "C" int kb_tpe_score_select(kb_ctx *ctx, int64_t n_cand, const double *cand, int64_t index_offset,
                                    int64_t *out_index, double *out_value, double *out_score) {
     if (!ctx) return KB_ERR_INVALID;
@@ -1275,8 +1298,11 @@ extern "C" int kb_tpe_score_select(kb_ctx *ctx, int64_t n_cand, const double *ca
     KbDeviceGuard g(ctx->device);
     int rc = tpe_precheck(ctx, n_cand, cand, "kb_tpe_score_select");
     if (rc) return rc;
-    if ((rc = tpe_run_host(ctx, n_cand, cand, index_offset, true, nullptr))) return rc;
-    return tpe_finish_selection(ctx, index_offset, out_index, out_value, out_score, ctx->stream);
+    for (int attempt = 0;; attempt++) {
+        rc = tpe_run_host(ctx, n_cand, cand, index_offset, true, nullptr);
+        if (!rc) rc = tpe_finish_selection(ctx, index_offset, out_index, out_value, out_score, ctx->stream);
+        if (!tpe_retry_overflow(ctx, rc, attempt)) return rc;
+    }
 }
 
 extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const double *cand_device, int64_t index_offset,
@@ -1288,14 +1314,17 @@ extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const dou
     if (rc) return rc;
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
     const int64_t rows = n_cand < KB_CHUNK_ROWS ? (n_cand > 0 ? n_cand : 1) : KB_CHUNK_ROWS;
-    if ((rc = tpe_ensure_scratch(ctx, rows, n_cand, false, false))) return rc;
-    if ((rc = tpe_reset_selection(ctx, s))) return rc;
-    const int64_t cap = ctx->chunk_cap;
-    for (int64_t off = 0; off < n_cand; off += cap) {
-        const int n = (int)(n_cand - off < cap ? n_cand - off : cap);
-        if ((rc = tpe_launch_chunk(ctx, cand_device + (size_t)off * ctx->D, n, index_offset + off, off, true, nullptr, s))) return rc;
+    for (int attempt = 0;; attempt++) {
+        if ((rc = tpe_ensure_scratch(ctx, rows, n_cand, false, false))) return rc;
+        if ((rc = tpe_reset_selection(ctx, s))) return rc;
+        const int64_t cap = ctx->chunk_cap;
+        for (int64_t off = 0; off < n_cand; off += cap) {
+            const int n = (int)(n_cand - off < cap ? n_cand - off : cap);
+            if ((rc = tpe_launch_chunk(ctx, cand_device + (size_t)off * ctx->D, n, index_offset + off, off, true, nullptr, s))) return rc;
+        }
+        rc = tpe_finish_selection(ctx, index_offset, out_index, out_value, out_score, s);
+        if (!tpe_retry_overflow(ctx, rc, attempt)) return rc;
     }
-    return tpe_finish_selection(ctx, index_offset, out_index, out_value, out_score, s);
 }
 
 // Full tpe.Sampler.Sample for every parameter: draw on the device (kb_tpe_sample.cu), score, select.
@@ -1342,13 +1371,17 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
     double *d_cand = ctx->d_suggest;
     int rc = kb_tpe_sample_into(ctx, n, seed, d_cand, s);
     const int64_t rows = n < KB_CHUNK_ROWS ? n : KB_CHUNK_ROWS;
-    if (!rc) rc = tpe_ensure_scratch(ctx, rows, n, false, false);
-    if (!rc) rc = tpe_reset_selection(ctx, s);
-    const int64_t cap = ctx->chunk_cap;
-    for (int64_t off = 0; !rc && off < n; off += cap) {
-        const int m = (int)(n - off < cap ? n - off : cap);
-        rc = tpe_launch_chunk(ctx, d_cand + (size_t)off * ctx->D, m, off, off, true, nullptr, s);
+    for (int attempt = 0; !rc; attempt++) {
+        rc = tpe_ensure_scratch(ctx, rows, n, false, false);
+        if (!rc) rc = tpe_reset_selection(ctx, s);
+        const int64_t cap = ctx->chunk_cap;
+        for (int64_t off = 0; !rc && off < n; off += cap) {
+            const int m = (int)(n - off < cap ? n - off : cap);
+            rc = tpe_launch_chunk(ctx, d_cand + (size_t)off * ctx->D, m, off, off, true, nullptr, s);
+        }
+        if (!rc) rc = tpe_finish_selection(ctx, 0, nullptr, out_value, nullptr, s);
+        if (!tpe_retry_overflow(ctx, rc, attempt)) break;
+        rc = KB_OK;
     }
-    if (!rc) rc = tpe_finish_selection(ctx, 0, nullptr, out_value, nullptr, s);
     return rc;
 }
