@@ -316,7 +316,10 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
             if (tid < off) s_red[tid] = fmax(s_red[tid], s_red[tid + off]);
             __syncthreads();
         }
-        if (tid == 0 && !(s_red[0] < 1e-6)) dm.qf_h0[side] = -1.f;
+        // ... and when the bin is so wide against sigma that a component further than YMAX still matters: the kernel
+        // clamps tau there, which is only harmless while erfc(YMAX - h) is negligible (found by the randomised tests:
+        // a step-3 integer on a range of 7 with 260 observations has h = 15)
+        if (tid == 0 && (!(s_red[0] < 1e-6) || h > KB_QF_YMAX - 4.6)) dm.qf_h0[side] = -1.f;
         __syncthreads();
     }
     // look-up class (see KbDim::lut): bin integral of a floor-sigma component at every integer grid offset

@@ -6,8 +6,11 @@ import pytest
 import katib_b200 as kb
 from test_gpu_tpe import make_history, oracle_scores, rel_err, sample_candidates
 
+import os
+
 pytestmark = pytest.mark.gpu
 KB_OPT_MERGE_DUPLICATES, KB_OPT_PRUNE_FAR = 1, 2
+N_SEEDS = int(os.environ.get("KB_FUZZ_SEEDS", "40"))  # KB_FUZZ_SEEDS=300 for a longer hunt
 
 
 def random_space(rng):
@@ -39,7 +42,7 @@ def random_space(rng):
     return dict(kinds=kinds, lows=lows, highs=highs, steps=steps, nch=nch)
 
 
-@pytest.mark.parametrize("seed", range(12))
+@pytest.mark.parametrize("seed", range(N_SEEDS))
 def test_all_scoring_variants_agree_with_the_oracle(seed):
     rng = np.random.Generator(np.random.PCG64(1000 + seed))
     sp = random_space(rng)
@@ -69,7 +72,7 @@ def test_all_scoring_variants_agree_with_the_oracle(seed):
     ctx.close()
 
 
-@pytest.mark.parametrize("seed", range(8))
+@pytest.mark.parametrize("seed", range(max(8, N_SEEDS // 2)))
 def test_fused_and_staged_suggest_agree_on_random_spaces(seed, monkeypatch):
     rng = np.random.Generator(np.random.PCG64(2000 + seed))
     sp = random_space(rng)
