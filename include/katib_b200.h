@@ -116,8 +116,8 @@ int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, double *w, doubl
 /* Score every candidate: scores[i*n_params + d] = log l(x) - log g(x) (FP32 arithmetic, FP64
  * accumulation) -- tpe.Sampler.gmmLogPDF / categoricalLogPDF on a caller-supplied
  * candidate set.  cand[n_cand x n_params] row-major, in the sampler's working domain: UNIFORM /
- * INT / STEP_INT as is, DISCRETE shifted by -low (goptuna shifts to [0, high-low]), CATEGORICAL
- * the choice index. */
+ * INT as is, DISCRETE and STEP_INT shifted by -low (sampleDiscreteUniform shifts to [0, high-low]
+ * so that rounding to the step lands on the grid {low + k step}), CATEGORICAL the choice index. */
 int kb_tpe_scores(kb_ctx *ctx, int64_t n_cand, const double *cand, double *scores);
 
 /* tpe.Sampler.compare on a caller-supplied candidate set, per parameter: index of the winning
@@ -177,8 +177,10 @@ int kb_sobol_fill_device(kb_ctx *ctx, int dim, uint64_t first_index, int64_t n_p
 int kb_cmaes_create(kb_ctx *ctx, int n, const double *mean, double sigma, int popsize,
                     const double *lo, const double *hi);
 /* Optimizer.Ask() lam times in one batch: x[k*n+i] = m_i + sigma*(B diag(D) z_k)_i.  z[lam x n]
- * row-major supplied by the caller (NULL: drawn on the device, Philox keyed by seed).  No
- * resampling; out-of-bounds coordinates are clipped when bounds exist (repairInfeasibleParams). */
+ * row-major supplied by the caller (NULL: drawn on the device, Philox keyed by seed).  With bounds:
+ * caller-supplied z is never redrawn, out-of-bounds coordinates are clipped (repairInfeasibleParams);
+ * device-drawn z is redrawn for an infeasible row up to 100 times and only then clipped, as the
+ * cmaes library's ask() does. */
 int kb_cmaes_ask(kb_ctx *ctx, int lam, const double *z, uint64_t seed, double *x);
 /* Optimizer.Tell(solutions): x[popsize x n] row-major, f[popsize] lower is better.
  * With a communicator of W ranks (kb_comm_init) the population is sharded by rows: every rank creates the optimiser

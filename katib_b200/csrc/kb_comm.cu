@@ -29,9 +29,16 @@ static KbNccl *nccl_api() {
     static KbNccl api;
     static std::once_flag once;
     std::call_once(once, [] {
-        const char *names[] = {"libnccl.so.2", "libnccl.so", nullptr};
+        // KB_NCCL_LIBRARY names the library to load instead (a deployment with its own NCCL build; the tests use it
+        // to reach the "not found" path)
+        const char *over = getenv("KB_NCCL_LIBRARY");
+        const char *names[] = {over && over[0] ? over : "libnccl.so.2", over && over[0] ? nullptr : "libnccl.so", nullptr};
         for (int i = 0; names[i] && !api.handle; i++) api.handle = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
-        if (!api.handle) { api.why = dlerror() ? dlerror() : "libnccl.so.2 not found"; return; }
+        if (!api.handle) {
+            const char *e = dlerror();  // one call: dlerror() clears the state it returns
+            api.why = e ? e : "libnccl.so.2 not found";
+            return;
+        }
         api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.handle, "ncclGetUniqueId");
         api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.handle, "ncclCommInitRank");
         api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");

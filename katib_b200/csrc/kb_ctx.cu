@@ -56,6 +56,7 @@ extern "C" int kb_create(int device, kb_ctx **out) {
         cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming);
     }
+    cudaEventCreateWithFlags(&ctx->ev_build, cudaEventDisableTiming);
     *out = ctx;
     return KB_OK;
 }
@@ -77,6 +78,7 @@ extern "C" int kb_destroy(kb_ctx *ctx) {
             if (ctx->ev_h2d[i]) cudaEventDestroy(ctx->ev_h2d[i]);
             if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
         }
+        if (ctx->ev_build) cudaEventDestroy(ctx->ev_build);
         prof_drain(ctx);
         for (auto e : ctx->prof_pool) cudaEventDestroy(e);
         if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -170,8 +172,10 @@ extern "C" int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, cons
                     if (!step || !(step[d] > 0))
                         return kb_fail(ctx, KB_ERR_INVALID, "kb_space_set: param %d: step must be > 0", d);
                     k.q = step[d];
-                    if (k.kind == KB_STEP_INT) { k.lo = lo - 0.5 * k.q; k.hi = hi + 0.5 * k.q; k.shift = 0; }
-                    else { k.lo = 0 - 0.5 * k.q; k.hi = (hi - lo) + 0.5 * k.q; k.shift = lo; }
+                    // sampleStepInt goes through sampleDiscreteUniform like DISCRETE: the range is shifted to
+                    // [0, high - low] so that rounding to multiples of the step lands on the grid {low + k step}
+                    // whatever low is (random_fill_kernel and the Sobol mapping use the same grid)
+                    k.lo = 0 - 0.5 * k.q; k.hi = (hi - lo) + 0.5 * k.q; k.shift = lo;
                     break;
                 }
                 default: return kb_fail(ctx, KB_ERR_INVALID, "kb_space_set: param %d: unknown kind %d", d, k.kind);

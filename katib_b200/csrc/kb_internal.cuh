@@ -126,6 +126,7 @@ struct kb_ctx {
     bool history_ready = false;
     bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
     bool tpe_prune = false;          // KB_OPT_PRUNE_FAR
+    bool quant_attr_set = false;     // dynamic shared-memory limit of the quantised score kernels raised
     float2 *d_stage_sorted = nullptr;  // [n_cont][chunk] stage_cont in bucket order (pruned scoring)
     int32_t *d_perm = nullptr;         // [n_cont][chunk] chunk-local index of the candidate at each sorted position
     int32_t *d_bucket = nullptr;       // [n_cont][KB_PRUNE_BUCKETS] histogram / running offsets
@@ -151,6 +152,7 @@ struct kb_ctx {
     double *d_suggest = nullptr;     // candidates drawn by kb_tpe_suggest (grow-only)
     int64_t suggest_cap = 0;
     cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    cudaEvent_t ev_build = nullptr;  // recorded on `stream` after every history build; caller streams wait on it
 
     uint32_t *d_sobol_v = nullptr;   // [32][KB_SOBOL_MAX_DIM] direction numbers, bit-major
 
@@ -202,6 +204,13 @@ struct KbDeviceGuard {
     explicit KbDeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
     ~KbDeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
+
+// A caller-supplied stream is not ordered after work queued on the context's own (non-blocking) stream: make it wait for
+// the most recent history build before anything on it reads the tables.
+static inline cudaError_t kb_order_after_build(kb_ctx *ctx, cudaStream_t s) {
+    if (s == ctx->stream || !ctx->ev_build) return cudaSuccess;
+    return cudaStreamWaitEvent(s, ctx->ev_build, 0);
+}
 
 // cross-file entry points
 int kb_tpe_free(kb_ctx *ctx);

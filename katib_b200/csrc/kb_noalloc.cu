@@ -73,8 +73,10 @@ noalloc_fold_kernel(unsigned char *scratch, int K0, const double *w0, const doub
     const double p_accept = s_red[0];
     __syncthreads();
     double lmax = -INFINITY;
-    for (int j = tid; j < K; j += NA_FOLD_THREADS)
-        lmax = fmax(lmax, log(w[j] / (sqrt(2.0 * M_PI) * sg[j]) / p_accept));
+    for (int j = tid; j < K; j += NA_FOLD_THREADS) {
+        const double s = sg[j] > NA_EPS ? sg[j] : NA_EPS;  // the same floor the exponent uses below
+        lmax = fmax(lmax, log(w[j] / (sqrt(2.0 * M_PI) * s) / p_accept));
+    }
     s_red[tid] = lmax;
     __syncthreads();
     for (int off = NA_FOLD_THREADS / 2; off > 0; off >>= 1) {
@@ -93,7 +95,7 @@ noalloc_fold_kernel(unsigned char *scratch, int K0, const double *w0, const doub
             const double ml = mun - (double)mh;
             const double s = sg[j] > NA_EPS ? sg[j] : NA_EPS;
             const float c = (float)(sqrt(0.5 * LOG2E) * (high - low) / s);
-            const double lc = log(w[j] / (sqrt(2.0 * M_PI) * sg[j]) / p_accept);
+            const double lc = log(w[j] / (sqrt(2.0 * M_PI) * s) / p_accept);
             const float mc = (float)(-ml * (double)c), kk = (float)((lc - L) * LOG2E);
             A = make_float4(-mh, -mh, c, c);
             B = make_float4(mc, mc, kk, kk);
@@ -156,7 +158,13 @@ noalloc_score_kernel(const unsigned char *scratch, const double *__restrict__ ca
             }
         }
 #pragma unroll
-        for (int r = 0; r < NA_R; r++) logS[side][r] = log((double)Shi[r] + (double)Slo[r]) + hdr->L[side];
+        for (int r = 0; r < NA_R; r++) {
+            // A candidate more than ~13 sigma from every component underflows the FP32 sum; the floor keeps the
+            // logarithm finite (the score then reads L_below - L_above instead of NaN).  Tables that come from
+            // kb_tpe_get_parzen never get here: their prior component spans the whole range.
+            const double S = fmax((double)Shi[r] + (double)Slo[r], 1e-300);
+            logS[side][r] = log(S) + hdr->L[side];
+        }
     }
 #pragma unroll
     for (int r = 0; r < NA_R; r++) {

@@ -566,7 +566,9 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
         KB_LAUNCH_CHECK(ctx);
     }
     // K / Kpad are known on the host (n_side + 1); p_accept and L stay on the device (kb_tpe_get_parzen fetches them),
-    // so the call returns without synchronising: the kernels above are simply ordered before any scoring launch
+    // so the call returns without synchronising: on the context's stream the kernels above are simply ordered before
+    // any scoring launch; a *_device entry point given another stream waits on ev_build (kb_order_after_build)
+    KB_CUDA(ctx, cudaEventRecord(ctx->ev_build, s));
     for (int d = 0; d < D; d++) {
         KbDim &k = ctx->h_dims[(size_t)d];
         for (int side = 0; side < 2; side++) {

@@ -76,6 +76,7 @@ extern "C" int kb_tpe_sample_candidates(kb_ctx *ctx, int64_t n, uint64_t seed, d
     if (n > 0 && !cand_host && !cand_device) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_sample_candidates: no output buffer");
     if (n == 0) return KB_OK;
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    KB_CUDA(ctx, kb_order_after_build(ctx, s));
     double *d_out = cand_device;
     if (!d_out) KB_CUDA(ctx, cudaMalloc(&d_out, sizeof(double) * (size_t)n * ctx->D));
     int rc = sample_launch(ctx, n, seed, d_out, s);

@@ -933,14 +933,10 @@ tpe_pick_kernel(const KbDim *__restrict__ dims, const KbSelect *__restrict__ sel
         w.score = best.score;
         w.index = best.idx == ~0ull ? -1 : (long long)best.idx;
         double v = best.x;
-        if (dm.kind == KB_DISCRETE) {  // sampleDiscreteUniform: shift back and clamp
+        if (dm.kind == KB_DISCRETE || dm.kind == KB_STEP_INT) {  // sampleDiscreteUniform: shift back and clamp
             v = v + dm.shift;
             v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         }
-        // sampleStepInt rounds to multiples of the step on [low - step/2, high + step/2] WITHOUT the shift: when
-        // high - low is not a multiple of the step the rounded value can pass `high` (or `low`); it is clamped here so
-        // that a suggestion never leaves the declared range (a superset of the restated goptuna rule)
-        if (dm.kind == KB_STEP_INT) v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         w.value = v;
         win[d] = w;
     }
@@ -1005,14 +1001,10 @@ tpe_suggest_small_kernel(const KbDim *__restrict__ dims, int n, uint64_t seed, K
         w.score = s_bs[0];
         w.index = b < n ? (long long)b : -1;
         double v = b < n ? s_x[b] : 0.0;
-        if (dm.kind == KB_DISCRETE) {  // sampleDiscreteUniform: shift back and clamp
+        if (dm.kind == KB_DISCRETE || dm.kind == KB_STEP_INT) {  // sampleDiscreteUniform: shift back and clamp
             v = v + dm.shift;
             v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         }
-        // sampleStepInt rounds to multiples of the step on [low - step/2, high + step/2] WITHOUT the shift: when
-        // high - low is not a multiple of the step the rounded value can pass `high` (or `low`); it is clamped here so
-        // that a suggestion never leaves the declared range (a superset of the restated goptuna rule)
-        if (dm.kind == KB_STEP_INT) v = fmin(fmax(v, dm.ext_lo), dm.ext_hi);
         if (dm.kind == KB_CATEGORICAL) {
             int c = (int)v;
             v = (double)(c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c));
@@ -1313,6 +1305,7 @@ extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const dou
     int rc = tpe_precheck(ctx, n_cand, cand_device, "kb_tpe_score_select_device");
     if (rc) return rc;
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    KB_CUDA(ctx, kb_order_after_build(ctx, s));
     const int64_t rows = n_cand < KB_CHUNK_ROWS ? (n_cand > 0 ? n_cand : 1) : KB_CHUNK_ROWS;
     for (int attempt = 0;; attempt++) {
         if ((rc = tpe_ensure_scratch(ctx, rows, n_cand, false, false))) return rc;

@@ -56,3 +56,17 @@ def test_create_fails_loudly_without_gpu(so):
     with pytest.raises(kb.KbError) as e:
         kb.Context(0)
     assert "no CPU path" in str(e.value)
+
+
+def test_missing_nccl_is_an_error_message_not_a_crash(so):
+    """kb_comm_unique_id needs no GPU, only libnccl: with a library name that cannot be loaded it must return
+    KB_ERR_COMM with the loader's message (it used to read dlerror() twice and build a std::string from NULL)."""
+    import sys
+    code = ("import ctypes, sys; L = ctypes.CDLL(%r); buf = ctypes.create_string_buffer(128); "
+            "rc = L.kb_comm_unique_id(buf); L.kb_last_error.restype = ctypes.c_char_p; "
+            "print(rc, L.kb_last_error(None).decode())") % so
+    env = dict(os.environ, KB_NCCL_LIBRARY="libnccl_that_does_not_exist.so.9")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=120)
+    assert out.returncode == 0, out.stderr[-500:]
+    rc, msg = out.stdout.split(None, 1)
+    assert int(rc) == -4 and "libnccl_that_does_not_exist" in msg

@@ -46,8 +46,6 @@ def working_domain(k, lo, hi, st):
         return lo, hi, 0.0, 0.0
     if k == kb.KB_INT:
         return lo - 0.5, hi + 0.5, 1.0, 0.0
-    if k == kb.KB_STEP_INT:
-        return lo - 0.5 * st, hi + 0.5 * st, st, 0.0
     return -0.5 * st, (hi - lo) + 0.5 * st, st, lo
 
 
@@ -258,7 +256,7 @@ def test_edges_empty_history_empty_candidates_wide_space(ctx):
     nc = 700
     cand = rng.uniform(-1, 2, (nc, D))
     cand[:, 298] = np.floor(rng.uniform(0, 4096, nc))
-    cand[:, 299] = -50 + 5 * np.floor(rng.uniform(0, 21, nc))
+    cand[:, 299] = 5 * np.floor(rng.uniform(0, 21, nc))  # working domain of STEP_INT: shifted by -low
     got = ctx.tpe_scores(cand)
     idx = ctx.tpe_score_select(cand)[0]
     for d in (0, 150, 297):
@@ -266,5 +264,5 @@ def test_edges_empty_history_empty_candidates_wide_space(ctx):
         assert rel_err(got[:, d], ref) < TOL and idx[d] == b
     ref, b = O.tpe_score_categorical(cand[:, 298], vals[:, 298], loss, 4096)
     assert rel_err(got[:, 298], ref) < 1e-12 and idx[298] == b
-    ref, b = O.tpe_score_numeric(cand[:, 299], vals[:, 299], loss, -52.5, 52.5, 5.0)
+    ref, b = O.tpe_score_numeric(cand[:, 299], vals[:, 299] + 50.0, loss, -2.5, 102.5, 5.0)
     assert rel_err(got[:, 299], ref) < TOL and idx[299] == b

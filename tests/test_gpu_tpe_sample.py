@@ -120,3 +120,22 @@ def test_fused_small_suggest_equals_the_staged_pipeline(n_trials, n_cand, monkey
         b = ctx.tpe_suggest(n_cand, seed)
         assert np.array_equal(a, b), (seed, a, b)
     ctx.close()
+
+
+def test_step_int_suggestions_stay_on_the_declared_grid():
+    """STEP_INT with low not a multiple of the step (low = 1, step = 2): suggestions are {1, 3, 5, 7, 9}, the grid that
+    kb_random_fill and the Sobol mapping use -- sampleStepInt shifts the range to [0, high - low] before rounding."""
+    rng = np.random.Generator(np.random.PCG64(5))
+    ctx = kb.Context(0)
+    ctx.space_set([kb.KB_STEP_INT, kb.KB_STEP_INT], [1, -7], [9, 8], [2, 3])
+    n = 60
+    vals = np.stack([1 + 2 * np.floor(rng.uniform(0, 5, n)), -7 + 3 * np.floor(rng.uniform(0, 6, n))], axis=1)
+    loss = (vals[:, 0] - 5) ** 2 + np.abs(vals[:, 1] - 2) + rng.normal(0, 0.1, n)
+    ctx.tpe_set_history(vals, loss)
+    for n_ei in (24, 3000):  # the fused small-problem kernel and the staged pipeline
+        for seed in range(6):
+            v = ctx.tpe_suggest(n_ei, seed)
+            assert v[0] in (1, 3, 5, 7, 9) and v[1] in (-7, -4, -1, 2, 5, 8), (n_ei, seed, v)
+    r = ctx.random_fill(seed=3, first=0, n=500)
+    assert set(np.unique(r[:, 0])) <= {1, 3, 5, 7, 9} and set(np.unique(r[:, 1])) <= {-7, -4, -1, 2, 5, 8}
+    ctx.close()
