@@ -251,6 +251,13 @@ int kb_peak_measure(kb_ctx *ctx, int which, double *out);
  * 4 sobol_fill  5 tpe_build  6 tpe_sample  7 cmaes_ask  8 cmaes_tell  9 eigh  10 collective  11 dgemm (DMMA) */
 int kb_profile(kb_ctx *ctx, int enable);
 int kb_profile_read(kb_ctx *ctx, int kernel_class, double *ms_total, int64_t *launches);
+/* Worst error of the FP32 scoring pipeline over a candidate set in HBM (same layout as kb_tpe_score_select_device):
+ * out_max_err[d] = max_i |score32(i,d) - score64(i,d)| / max(1, |score64(i,d)|) for numeric parameters (0 for
+ * categorical ones), where score32 is what selection sees (the pipeline's score rounded to float) and score64 is the
+ * FP64 formula the winners are decided with, evaluated on the device for EVERY candidate.  Costs ~100 FP64
+ * operations per (candidate, component): minutes at the headline size.  The admission margins of the near-tie
+ * table must stay above these numbers. */
+int kb_tpe_score_error_device(kb_ctx *ctx, int64_t n_cand, const double *cand_device, double *out_max_err);
 /* number of kernels this library has launched on this ctx since creation */
 int64_t kb_launch_count(const kb_ctx *ctx);
 

@@ -70,6 +70,7 @@ def lib():
         "kb_tpe_score_select": ([vp, i64, vp, i64, vp, vp, vp], i32),
         "kb_tpe_score_select_device": ([vp, i64, vp, i64, vp, vp, vp, vp], i32),
         "kb_tpe_suggest": ([vp, i64, u64, vp], i32),
+        "kb_tpe_score_error_device": ([vp, i64, vp, vp], i32),
         "kb_tpe_sample_candidates": ([vp, i64, u64, vp, vp, vp], i32),
         "kb_sobol_fill": ([vp, i32, u64, i64, vp, vp, vp], i32),
         "kb_sobol_fill_device": ([vp, i32, u64, i64, vp, vp, vp, vp], i32),
@@ -284,6 +285,12 @@ class Context:
         self._ck(lib().kb_tpe_score_select_device(self._h, n, dev_ptr, index_offset, _ptr(idx), _ptr(val), _ptr(sc),
                                                   stream))
         return idx, val, sc
+
+    def tpe_score_error_device(self, n, dev_ptr):
+        """per-parameter worst |FP32-pipeline score - FP64 score| / max(1, |FP64 score|) over n candidates in HBM"""
+        out = np.zeros(self.D)
+        self._ck(lib().kb_tpe_score_error_device(self._h, n, dev_ptr, _ptr(out)))
+        return out
 
     def tpe_suggest(self, n_ei_candidates, seed):
         out = np.zeros(self.D)

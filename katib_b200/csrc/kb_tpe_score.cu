@@ -894,12 +894,17 @@ tpe_rescore_kernel(const KbDim *__restrict__ dims, const int *__restrict__ numer
 }
 
 // one CTA per parameter: best listed value (score desc, index asc); categorical winners decode their packed key
+// win[D] is the status row of the call: .index = 1 + the highest parameter whose near-tie table overflowed (0 = none).
+// It travels with the winners through the all-gather, so that every rank learns of an overflow on any rank.
 __global__ void __launch_bounds__(RS_THREADS)
 tpe_pick_kernel(const KbDim *__restrict__ dims, const KbSelect *__restrict__ sel, unsigned int slots,
-                const KbCand *__restrict__ list, const unsigned int *__restrict__ count, KbWinner *win, long long idx_base) {
+                const KbCand *__restrict__ list, const unsigned int *__restrict__ count, KbWinner *win, long long idx_base,
+                int D) {
     __shared__ KbCand s_best[RS_THREADS];
     const int d = blockIdx.x;
     const KbDim &dm = dims[d];
+    if (threadIdx.x == 0 && sel[d].overflow)
+        atomicMax(reinterpret_cast<unsigned long long *>(&win[D].index), (unsigned long long)(d + 1));
     KbWinner w;
     if (dm.kind == KB_CATEGORICAL) {
         if (threadIdx.x != 0) return;
@@ -1017,10 +1022,19 @@ tpe_suggest_small_kernel(const KbDim *__restrict__ dims, int n, uint64_t seed, K
 // pick the best of `world` gathered winner rows (score desc, index asc)
 __global__ void tpe_merge_kernel(const KbWinner *__restrict__ all, int world, int D, KbWinner *win) {
     const int d = blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= D) return;
+    if (d > D) return;
+    if (d == D) {  // status row: an overflow on any rank is an overflow of the call, on every rank
+        KbWinner st = all[D];
+        for (int r = 1; r < world; r++) {
+            const KbWinner o = all[(size_t)r * (D + 1) + D];
+            if (o.index > st.index) st = o;
+        }
+        win[D] = st;
+        return;
+    }
     KbWinner best = all[d];
     for (int r = 1; r < world; r++) {
-        KbWinner o = all[(size_t)r * D + d];
+        KbWinner o = all[(size_t)r * (D + 1) + d];
         if (o.index < 0) continue;
         if (best.index < 0 || o.score > best.score || (o.score == best.score && o.index < best.index)) best = o;
     }
@@ -1064,11 +1078,11 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
     const int D = ctx->D;
     if (!ctx->d_sel) {
         KB_CUDA(ctx, cudaMalloc(&ctx->d_sel, sizeof(KbSelect) * (size_t)D));
-        if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)D));  // the small path may have made these two
-        KB_CUDA(ctx, cudaMalloc(&ctx->d_win_all, sizeof(KbWinner) * (size_t)D * 64));
+        if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)(D + 1)));  // the small path may have made these two
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_win_all, sizeof(KbWinner) * (size_t)(D + 1) * 64));
         const size_t slots = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
         KB_CUDA(ctx, cudaMalloc(&ctx->d_tie_count, sizeof(unsigned int) * slots));
-        if (!sc->h_win) KB_CUDA(ctx, cudaMallocHost(&sc->h_win, sizeof(KbWinner) * (size_t)D));
+        if (!sc->h_win) KB_CUDA(ctx, cudaMallocHost(&sc->h_win, sizeof(KbWinner) * (size_t)(D + 1)));
         std::vector<int> slot_of((size_t)D, 0), numeric(slots, 0);
         for (int i = 0; i < ctx->n_cont; i++) slot_of[(size_t)ctx->cont_dims[(size_t)i]] = i;
         for (int i = 0; i < ctx->n_quant; i++) slot_of[(size_t)ctx->quant_dims[(size_t)i]] = i;
@@ -1155,8 +1169,10 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
         dim3 grid((unsigned)((n + SQ_TILE - 1) / SQ_TILE), (unsigned)ctx->n_quant);
         KbProf pf(ctx, 2, s);
         const size_t lut_bytes = (size_t)KB_LUT_MAX * 32 * sizeof(float);  // bank-replicated look-up table
-        // per device, and cheap: set on every launch rather than tracked (static 32 KB + dynamic 32 KB > the 48 KB default)
-        KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lut_bytes));
+        if (!ctx->quant_attr_set) {  // once per context (static 32 KB + dynamic 32 KB > the 48 KB default)
+            KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lut_bytes));
+            ctx->quant_attr_set = true;
+        }
         tpe_score_quant_kernel<<<grid, SC_THREADS, lut_bytes, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant, ctx->chunk_cap,
                                                            n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
@@ -1169,6 +1185,7 @@ static int tpe_reset_selection(kb_ctx *ctx, cudaStream_t s) {
     KB_CUDA(ctx, cudaMemsetAsync(ctx->d_sel, 0, sizeof(KbSelect) * (size_t)ctx->D, s));
     KB_CUDA(ctx, cudaMemsetAsync(ctx->d_tie, 0xFF, sizeof(KbTie) * slots * ctx->tie_slots, s));
     KB_CUDA(ctx, cudaMemsetAsync(ctx->d_tie_count, 0, sizeof(unsigned int) * slots, s));
+    KB_CUDA(ctx, cudaMemsetAsync(ctx->d_win + ctx->D, 0, sizeof(KbWinner), s));  // status row (tpe_pick_kernel)
     return KB_OK;
 }
 
@@ -1189,26 +1206,27 @@ static int tpe_finish_selection(kb_ctx *ctx, long long idx_base, int64_t *out_in
             KB_LAUNCH_CHECK(ctx);
         }
         tpe_pick_kernel<<<D, RS_THREADS, 0, s>>>(ctx->d_dims, ctx->d_sel, ctx->tie_slots, (const KbCand *)ctx->d_tie_list,
-                                                  ctx->d_tie_count, ctx->d_win, idx_base);
+                                                  ctx->d_tie_count, ctx->d_win, idx_base, D);
         KB_LAUNCH_CHECK(ctx);
     }
     int world = 1, rank = 0;
     kb_comm_world(ctx, &world, &rank);
     if (world > 1) {
+        // winners and the status row go through ONE collective: a rank whose near-tie table overflowed is seen by all
+        // ranks before any of them trusts the merged winners, and all of them repeat the pass (or fail) together
         if (world > 64) return kb_fail(ctx, KB_ERR_UNSUPPORTED, "world > 64");
-        int rc = kb_comm_allgather(ctx, ctx->d_win, ctx->d_win_all, sizeof(KbWinner) * (size_t)D, s);
+        KbProf pf(ctx, 10, s);
+        int rc = kb_comm_allgather(ctx, ctx->d_win, ctx->d_win_all, sizeof(KbWinner) * (size_t)(D + 1), s);
         if (rc) return rc;
-        tpe_merge_kernel<<<(D + 127) / 128, 128, 0, s>>>(ctx->d_win_all, world, D, ctx->d_win);
+        tpe_merge_kernel<<<(D + 1 + 127) / 128, 128, 0, s>>>(ctx->d_win_all, world, D, ctx->d_win);
         KB_LAUNCH_CHECK(ctx);
     }
-    KB_CUDA(ctx, cudaMemcpyAsync(sc->h_win, ctx->d_win, sizeof(KbWinner) * (size_t)D, cudaMemcpyDeviceToHost, s));
-    std::vector<KbSelect> hsel((size_t)D);
-    KB_CUDA(ctx, cudaMemcpyAsync(hsel.data(), ctx->d_sel, sizeof(KbSelect) * (size_t)D, cudaMemcpyDeviceToHost, s));
+    KB_CUDA(ctx, cudaMemcpyAsync(sc->h_win, ctx->d_win, sizeof(KbWinner) * (size_t)(D + 1), cudaMemcpyDeviceToHost, s));
     KB_CUDA(ctx, cudaStreamSynchronize(s));
+    if (sc->h_win[D].index > 0)
+        return kb_fail(ctx, KB_ERR_OVERFLOW, "kb_tpe_score_select: near-tie table of parameter %lld overflowed (%u slots%s)",
+                       sc->h_win[D].index - 1, ctx->tie_slots, world > 1 ? "; on at least one rank" : "");
     for (int d = 0; d < D; d++) {
-        if (hsel[(size_t)d].overflow)
-            return kb_fail(ctx, KB_ERR_OVERFLOW, "kb_tpe_score_select: near-tie table of parameter %d overflowed (%u slots)", d,
-                           ctx->tie_slots);
         if (out_index) out_index[d] = sc->h_win[d].index;
         if (out_value) out_value[d] = sc->h_win[d].value;
         if (out_score) out_score[d] = sc->h_win[d].score;
@@ -1272,13 +1290,13 @@ extern "C" int kb_tpe_scores(kb_ctx *ctx, int64_t n_cand, const double *cand, do
 // The near-tie table is sized for the usual case (a handful of distinct values near the maximum).  A flat score
 // landscape -- e.g. a history so small that both mixtures are the prior alone -- puts every distinct candidate value
 // within the margin; then the pass is repeated with a table 16 times larger (twice at most, up to 2^20 slots per
-// parameter) before KB_ERR_OVERFLOW is reported.  Single rank only: a retry would unbalance the collective.
+// parameter) before KB_ERR_OVERFLOW is reported.  With a communicator the overflow status is part of the gathered
+// winner rows (tpe_pick_kernel / tpe_merge_kernel), so every rank takes the same decision here and the collectives
+// stay balanced; the decision must not depend on this rank's own table size (shards may differ by a row), only on
+// the attempt count.
 static bool tpe_retry_overflow(kb_ctx *ctx, int rc, int attempt) {
-    if (rc != KB_ERR_OVERFLOW || attempt >= 2 || ctx->tie_slots >= KB_TIE_SLOTS_MAX) return false;
-    int world = 1, rank = 0;
-    kb_comm_world(ctx, &world, &rank);
-    if (world > 1) return false;
-    const unsigned long long next = (unsigned long long)ctx->tie_slots * 16ull;
+    if (rc != KB_ERR_OVERFLOW || attempt >= 2) return false;
+    const unsigned long long next = (unsigned long long)std::max(ctx->tie_slots, (unsigned int)KB_TIE_SLOTS_MIN) * 16ull;
     ctx->tie_slots_floor = next > KB_TIE_SLOTS_MAX ? KB_TIE_SLOTS_MAX : (unsigned int)next;
     return true;
 }
@@ -1343,8 +1361,8 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
         }
         const char *off = getenv("KB_SUGGEST_SMALL");
         if (world == 1 && n <= SM_MAX_CAND && n * kmax <= (1 << 18) && !(off && off[0] == '0')) {
-            if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)ctx->D));
-            if (!ctx->h_win) KB_CUDA(ctx, cudaMallocHost(&ctx->h_win, sizeof(KbWinner) * (size_t)ctx->D));
+            if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)(ctx->D + 1)));
+            if (!ctx->h_win) KB_CUDA(ctx, cudaMallocHost(&ctx->h_win, sizeof(KbWinner) * (size_t)(ctx->D + 1)));
             {
                 KbProf pf(ctx, 3, s);
                 tpe_suggest_small_kernel<<<(unsigned)ctx->D, SM_THREADS, 0, s>>>(ctx->d_dims, (int)n, seed, ctx->d_win);
@@ -1377,4 +1395,65 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
         rc = KB_OK;
     }
     return rc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// measurement helper: worst FP32-path score error of a candidate set, FP64 side computed on the device
+// ---------------------------------------------------------------------------------------------------------
+// one warp per (candidate, numeric parameter): rescore_value (the FP64 decision formula, oracle-tested) against the
+// score the FP32 pipeline produced for the same pair, as selection sees it (rounded to float)
+__global__ void __launch_bounds__(RS_THREADS)
+tpe_score_error_kernel(const KbDim *__restrict__ dims, const int *__restrict__ numeric_dims, int n_numeric, int D, int n,
+                       const double *__restrict__ cand, const double *__restrict__ scores, unsigned long long *err_bits) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long total = (long long)n * n_numeric;
+    for (long long e = (long long)blockIdx.x * (RS_THREADS / 32) + warp; e < total; e += (long long)gridDim.x * (RS_THREADS / 32)) {
+        const int slot = (int)(e % n_numeric);
+        const long long i = e / n_numeric;
+        const int d = numeric_dims[slot];
+        const double ref = rescore_value(dims[d], cand[(size_t)i * D + d], lane);
+        if (lane == 0) {
+            const double got = (double)(float)scores[(size_t)i * D + d];
+            double err = fabs(got - ref) / fmax(1.0, fabs(ref));
+            if (!(err == err)) err = INFINITY;
+            atomicMax(&err_bits[d], (unsigned long long)__double_as_longlong(err));  // err >= 0: bit order = value order
+        }
+    }
+}
+
+extern "C" int kb_tpe_score_error_device(kb_ctx *ctx, int64_t n_cand, const double *cand_device, double *out_max_err) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    int rc = tpe_precheck(ctx, n_cand, cand_device, "kb_tpe_score_error_device");
+    if (rc) return rc;
+    if (!out_max_err) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_score_error_device: out_max_err is NULL");
+    const int D = ctx->D;
+    for (int d = 0; d < D; d++) out_max_err[d] = 0.0;
+    if (n_cand == 0 || ctx->n_numeric == 0) return KB_OK;
+    cudaStream_t s = ctx->stream;
+    const int64_t rows = std::min<int64_t>(n_cand, 1 << 20);
+    if ((rc = tpe_ensure_scratch(ctx, rows, n_cand, false, true))) return rc;
+    unsigned long long *d_err = nullptr;
+    KB_CUDA(ctx, cudaMalloc(&d_err, sizeof(unsigned long long) * (size_t)D));
+    cudaMemsetAsync(d_err, 0, sizeof(unsigned long long) * (size_t)D, s);
+    for (int64_t off = 0; off < n_cand && !rc; off += rows) {
+        const int n = (int)std::min<int64_t>(rows, n_cand - off);
+        rc = tpe_launch_chunk(ctx, cand_device + (size_t)off * D, n, off, off, false, ctx->d_scores_chunk, s);
+        if (rc) break;
+        tpe_score_error_kernel<<<148 * 8, RS_THREADS, 0, s>>>(ctx->d_dims, ctx->d_numeric_dims, ctx->n_numeric, D, n,
+                                                              cand_device + (size_t)off * D, ctx->d_scores_chunk, d_err);
+        ctx->launches++;
+        if (cudaGetLastError() != cudaSuccess) rc = kb_fail(ctx, KB_ERR_CUDA, "kb_tpe_score_error_device: launch failed");
+    }
+    std::vector<unsigned long long> h((size_t)D, 0ull);
+    if (!rc) {
+        cudaError_t e = cudaMemcpyAsync(h.data(), d_err, sizeof(unsigned long long) * (size_t)D, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) rc = kb_fail(ctx, KB_ERR_CUDA, "kb_tpe_score_error_device: %s", cudaGetErrorString(e));
+    }
+    cudaFree(d_err);
+    if (rc) return rc;
+    for (int d = 0; d < D; d++) memcpy(&out_max_err[d], &h[(size_t)d], sizeof(double));
+    return KB_OK;
 }
