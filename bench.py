@@ -32,6 +32,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 N_HISTORY = 10_000
+# admission margins of the near-tie table (kb_tpe_score.cu: KB_MARGIN_CONT / KB_MARGIN_QUANT)
+MARGIN_CONT, MARGIN_QUANT = 4e-6, 1.5e-5
 CAT_CHOICES = [2, 3, 4, 6, 8, 12, 16]
 
 
@@ -73,16 +75,22 @@ def workload_history(kinds, lows, highs, steps, nch, n=N_HISTORY, seed=5):
     return np.stack(cols, axis=1), loss
 
 
-def device_candidates(torch, kinds, lows, highs, steps, nch, n, seed, device):
+CAND_BLOCK = 1 << 20
+
+
+def device_candidates(torch, kinds, lows, highs, steps, nch, first, n, seed, device):
     """Synthetic candidates in the sampler's working domain, generated on the device by torch (plumbing):
-    uniform over each parameter's range; quantised parameters on their grid; categorical = choice index."""
+    uniform over each parameter's range; quantised parameters on their grid; categorical = choice index.
+    Rows [first, first + n) of ONE global candidate set: block b (2^20 rows) is drawn from its own generator seeded by
+    (seed, b), so a row's content depends only on its global index -- every sharding of the set scores the same rows
+    and must report the same winners."""
     import katib_b200 as kb
     g = torch.Generator(device=device)
-    g.manual_seed(seed)
     out = torch.empty((n, len(kinds)), dtype=torch.float64, device=device)
-    rows = 1 << 20
-    for r0 in range(0, n, rows):
-        m = min(rows, n - r0)
+    rows = CAND_BLOCK
+    for b in range(first // rows, (first + n + rows - 1) // rows):
+        g.manual_seed(seed * 1_000_003 + b)
+        m = rows
         u = torch.rand((m, len(kinds)), generator=g, device=device, dtype=torch.float64)
         for d, k in enumerate(kinds):
             if k == kb.KB_UNIFORM:
@@ -93,7 +101,8 @@ def device_candidates(torch, kinds, lows, highs, steps, nch, n, seed, device):
                 u[:, d] = steps[d] * torch.floor(u[:, d] * ((highs[d] - lows[d]) / steps[d] + 1))
             else:
                 u[:, d] = torch.floor(u[:, d] * nch[d])
-        out[r0:r0 + m] = u
+        g0, g1 = max(first, b * rows), min(first + n, (b + 1) * rows)  # the part of block b inside [first, first + n)
+        out[g0 - first:g1 - first] = u[g0 - b * rows:g1 - b * rows]
     return out
 
 
@@ -199,7 +208,11 @@ def main():
         if int(os.environ.get("RANK", "0")) == 0:
             bench_workloads.WORKLOADS[args.workload](args)
         return
-    os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "NONE")  # NCCL prints its version banner on stdout from level VERSION up; stdout carries one JSON line
+    # NCCL reports its communicators (rank count, transport) at level INFO; that log goes to stderr so that stdout keeps
+    # its one JSON line (NCCL's default sink is stdout)
+    os.environ.setdefault("NCCL_DEBUG", os.environ.get("KB_NCCL_DEBUG", "INFO"))
+    os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -258,7 +271,7 @@ def main():
     from katib_b200.sharding import shard_range
     offset, end = shard_range(n_total, world, rank)
     n_local = end - offset
-    cand = device_candidates(torch, kinds, lows, highs, steps, nch, n_local, 55 + rank, dev)
+    cand = device_candidates(torch, kinds, lows, highs, steps, nch, offset, n_local, 55, dev)
     torch.cuda.synchronize()
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
 
@@ -360,6 +373,69 @@ def main():
         ctx.tpe_set_option(2, 0)
         ctx.tpe_set_option(1, 0)
 
+    # ---- parity inside the bench (untimed): winners of a prefix of THIS candidate set against the CPU oracle, and the
+    # worst FP32-pipeline score error against the FP64 decision formula evaluated on the device for every pair
+    winners_vs_oracle, score_error = None, None
+    if rank == 0 and os.environ.get("KB_BENCH_PARITY", "1") == "1":
+        import _oracle as O
+        O.lib()
+        cores = os.cpu_count() or 1
+        n_pref = int(os.environ.get("KB_BENCH_PARITY_ROWS", str(65536 if cores >= 16 else 16384)))
+        n_pref = min(n_pref, n_local)
+        pref = cand[:n_pref].cpu().numpy()
+        pctx = kb.Context(local_rank)  # no communicator: rank 0 alone does this
+        pctx.space_set(kinds, lows, highs, steps, nch)
+        pctx.tpe_set_history(vals, loss)
+        got_idx = pctx.tpe_score_select_device(n_pref, cand.data_ptr(), offset)[0]
+        parts = np.array_split(np.arange(n_pref), cores)
+        scores = [None] * len(parts)
+
+        def work(k):
+            sc = np.empty((len(parts[k]), D))
+            for d, kd in enumerate(kinds):
+                if kd == kb.KB_CATEGORICAL:
+                    sc[:, d] = O.tpe_score_categorical(pref[parts[k], d], vals[:, d], loss, nch[d])[0]
+                elif kd == kb.KB_UNIFORM:
+                    sc[:, d] = O.tpe_score_numeric(pref[parts[k], d], vals[:, d], loss, lows[d], highs[d])[0]
+                elif kd == kb.KB_INT:
+                    sc[:, d] = O.tpe_score_numeric(pref[parts[k], d], vals[:, d], loss, lows[d] - 0.5, highs[d] + 0.5, 1.0)[0]
+                else:
+                    q = steps[d]
+                    sc[:, d] = O.tpe_score_numeric(pref[parts[k], d], vals[:, d] - lows[d], loss, -0.5 * q,
+                                                   (highs[d] - lows[d]) + 0.5 * q, q)[0]
+            scores[k] = sc
+        t0 = time.perf_counter()
+        ths = [threading.Thread(target=work, args=(k,)) for k in range(len(parts)) if len(parts[k])]
+        [t.start() for t in ths]
+        [t.join() for t in ths]
+        sc_all = np.concatenate([s for s in scores if s is not None], axis=0)
+        want_idx = [int(np.argmax(sc_all[:, d])) + offset for d in range(D)]  # argmax: first maximum
+        winners_vs_oracle = {"n": n_pref, "identical": bool([int(i) for i in got_idx] == want_idx),
+                             "oracle_s": time.perf_counter() - t0, "oracle_threads": len(ths),
+                             "note": "winners of the first n rows of this run's candidate set: kb_tpe_score_select_device vs "
+                                     "oracle/tpe.c (first maximum of the FP64 scores)"}
+        n_err = min(n_local, 1 << int(os.environ.get("KB_BENCH_ERR_LOG2", "21")))
+        t0 = time.perf_counter()
+        errs = pctx.tpe_score_error_device(n_err, cand.data_ptr())
+        pctx.close()
+        e_cont = float(max(errs[d] for d, kd in enumerate(kinds) if kd == kb.KB_UNIFORM))
+        e_quant = float(max(errs[d] for d, kd in enumerate(kinds) if kd in (kb.KB_INT, kb.KB_DISCRETE, kb.KB_STEP_INT)))
+        score_error = {"rows": n_err, "pairs": n_err * 30, "continuous": e_cont, "quantised": e_quant,
+                       "margin_continuous": MARGIN_CONT, "margin_quantised": MARGIN_QUANT,
+                       "margin_over_error": [MARGIN_CONT / max(e_cont, 1e-300), MARGIN_QUANT / max(e_quant, 1e-300)],
+                       "seconds": time.perf_counter() - t0,
+                       "note": "max |score32 - score64| / max(1, |score64|) over every (row, numeric parameter) pair of the first "
+                               "`rows` candidates, FP64 side = the decision formula on the device (kb_tpe_score_error_device); "
+                               "KB_BENCH_ERR_LOG2=26 covers the whole set (minutes) -- that run is kept in profiles/"}
+
+    # ---- secondary: BASELINE configs[1], [2], [3] on this GPU (rank 0), compact
+    secondary = None
+    if rank == 0 and os.environ.get("KB_BENCH_SECONDARY", "1") == "1":
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_workloads
+        host = None  # release the pinned slice before the Sobol block needs its own host array
+        secondary = bench_workloads.secondary_block(args, local_rank)
+
     def shutdown():
         # orderly exit on every rank: the library's NCCL communicator goes first, on all ranks together, then torch's
         torch.cuda.synchronize()
@@ -393,11 +469,12 @@ def main():
                                     "(the traffic is the candidate columns, read once)")
         if k == 2 and ms_k > 0:
             a = ce_quant / (ms_k * 1e-3) / 1e9
-            ent.update(bound="sfu", unit="G CDF-pair evals/s (2 exp = 2 MUFU.EX2 each, algorithmic)", achieved=a,
-                       peak=peaks["mufu_ex2_gops"] / 2, frac=a / (peaks["mufu_ex2_gops"] / 2), traffic=195.6e6 * launch_rows / float(1 << 20),
-                       note="frac > 1 is not an error: the peak is the SFU roofline of the erf formulation (2 exp per evaluation); "
-                            "on-grid components x on-grid candidates take the look-up class (1 LDS + 1 FFMA per evaluation, "
-                            "no SFU), which is bound by shared-memory load issue instead",
+            ent.update(bound="fp32", unit="G bin-integral evals/s (1 FP32 FMA lane-op each as executed: look-up class)", achieved=a,
+                       peak=peaks["fp32_gfma"], frac=a / peaks["fp32_gfma"], traffic=195.6e6 * launch_rows / float(1 << 20),
+                       note="every (candidate, component) pair of this workload is an on-grid pair: its bin integral is a table "
+                            "value times the component weight, one FP32 FMA lane-op; the bound is the FP32 FMA pipe "
+                            "(kb_peak_measure FFMA micro-kernel).  Against the erf formulation's SFU roofline (2 exp per "
+                            f"evaluation) the same rate is {a / (peaks['mufu_ex2_gops'] / 2):.2f}x",
                        traffic_note=f"dram read+write bytes per launch: 195.6 MB measured by ncu --set full on a 2^20-candidate launch, "
                                     f"scaled to this run's {launch_rows}-candidate launches")
         if k == 0 and ms_k > 0:
@@ -435,6 +512,7 @@ def main():
                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
            "merged_duplicates": merged, "pruned": pruned, "latency": latency,
+           "winners_vs_oracle": winners_vs_oracle, "score_error_max": score_error, "secondary": secondary,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
     print(json.dumps(out), flush=True)
     shutdown()

@@ -23,31 +23,31 @@ def _events(torch, stream):
 
 
 # ------------------------------------------------------------------------------------------------ configs[1]
-def sobol(args):
+def sobol(args, device=0, emit=True):
     """Sobol 64-dim x 2^24 points, f64, bit-exact vs the oracle; HBM-write bound (8.59 GB written)."""
     import torch
     import katib_b200 as kb
     import _oracle as O
-    ctx = kb.Context(0)
-    dev = torch.device("cuda", 0)
+    ctx = kb.Context(device)
+    dev = torch.device("cuda", device)
     dim, n = 64, 1 << (args.cand if args.cand != 26 else 24)
-    out = torch.empty((n, dim), dtype=torch.float64, device=dev)
+    out_t = torch.empty((n, dim), dtype=torch.float64, device=dev)
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
     for _ in range(args.warmup):
-        ctx.sobol_fill_device(dim, 0, n, out.data_ptr())
+        ctx.sobol_fill_device(dim, 0, n, out_t.data_ptr())
     torch.cuda.synchronize()
     ctx.profile(True)
     e0, e1 = _events(torch, stream)
     e0.record(stream)
     for _ in range(args.steps):
-        ctx.sobol_fill_device(dim, 0, n, out.data_ptr())
+        ctx.sobol_fill_device(dim, 0, n, out_t.data_ptr())
     e1.record(stream)
     e1.synchronize()
     ms = e0.elapsed_time(e1) / args.steps
     k_ms, k_n = ctx.profile_read(4)
     ctx.profile(False)
     golden = os.path.join(ROOT, "tests", "golden")
-    tail = out[-4096:].cpu().numpy()
+    tail = out_t[-4096:].cpu().numpy()
     exact = bool(np.array_equal(tail, O.sobol(golden, dim, n - 4096, 4096)))
     # end to end: host buffer through kb_sobol_fill (device fill + D2H of the whole block)
     host = np.empty((n, dim))
@@ -64,7 +64,7 @@ def sobol(args):
     bytes_alg = float(n) * dim * 8
     achieved = bytes_alg / (k_ms / k_n * 1e-3) / 1e9
     peak = _peaks_file()["hbm_gbs"]
-    print(json.dumps({
+    out = ({
         "metric": "sobol_points_per_s", "value": n / (ms * 1e-3), "unit": "points/s (64-dim f64)", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32 state -> f64", "data": "synthetic",
@@ -78,18 +78,22 @@ def sobol(args):
                      "kernel": "sobol_fill_kernel", "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy; of measured); "
                      f"write-only ceiling measured by kb_peak_measure here: {ctx.peak(3):.0f} GB/s"},
         "cpu_baseline": {"value": ns / cpu_s, "unit": "points/s", "cores": 1, "kind": "port",
-                         "sample": f"2^20 points x 64 dims, {cpu_s:.2f} s, oracle/sobol.c"}}))
+                         "sample": f"2^20 points x 64 dims, {cpu_s:.2f} s, oracle/sobol.c"}})
     ctx.close()
+    del out_t
+    if emit:
+        print(json.dumps(out))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ configs[2]
-def tpe20(args):
+def tpe20(args, device=0, emit=True):
     """TPE 20-dim continuous, 1k-trial history, 1M candidates per GetSuggestions, 1 GPU."""
     import torch
     import katib_b200 as kb
     import _oracle as O
-    ctx = kb.Context(0)
-    dev = torch.device("cuda", 0)
+    ctx = kb.Context(device)
+    dev = torch.device("cuda", device)
     rng = np.random.Generator(np.random.PCG64(3))
     D, n, nc = 20, 1000, 1_000_000 if args.cand == 26 else 1 << args.cand
     s = np.linspace(0.5, 4.0, D)
@@ -140,7 +144,7 @@ def tpe20(args):
     cpu_s = time.perf_counter() - t0
     ce = float(nc) * D * (26 + 976) * args.steps
     a = ce / (prof[1][0] * 1e-3) / 1e9
-    print(json.dumps({
+    out = ({
         "metric": "tpe_candidates_scored_per_s", "value": nc / (ms * 1e-3), "unit": "candidates/s", "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32 (hi/lo-split inputs; winners re-scored in f64)", "data": "synthetic",
@@ -154,16 +158,19 @@ def tpe20(args):
                      "kernels": [{"class": k, "ms_total": prof[k][0], "launches": prof[k][1]} for k in range(4)],
                      "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel, this GPU, this run (of measured)"},
         "cpu_baseline": {"value": m / cpu_s, "unit": "candidates/s", "cores": 1, "kind": "port",
-                         "sample": f"{m} candidates x 20 params x 1000-trial history, {cpu_s:.1f} s, oracle/tpe.c"}}))
+                         "sample": f"{m} candidates x 20 params x 1000-trial history, {cpu_s:.1f} s, oracle/tpe.c"}})
     ctx.close()
+    if emit:
+        print(json.dumps(out))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ configs[3]
-def cmaes(args):
+def cmaes(args, device=0, emit=True, cpu_tell_baseline=True):
     """CMA-ES 512-dim, popsize 4096, FP64; a step = one generation (ask + tell), objective evaluated by the harness."""
     import katib_b200 as kb
     import _oracle as O
-    ctx = kb.Context(0)
+    ctx = kb.Context(device)
     rng = np.random.Generator(np.random.PCG64(4))
     n, lam = 512, 4096
     gens = args.steps if args.steps > 3 else 20
@@ -172,12 +179,15 @@ def cmaes(args):
     fobj = lambda X: np.sum((X @ Q) ** 2 * scale, axis=1)
     m0 = np.full(n, 3.0)
     ctx.cmaes_create(m0, 2.0, lam, np.full(n, -5.0), np.full(n, 5.0))
-    opt = O.Cma(m0, 2.0, lam)
     Z = rng.normal(size=(lam, n))
     X = ctx.cmaes_ask(lam, Z); f = fobj(X)
-    t0 = time.perf_counter(); opt.tell(X, f); cpu_tell = time.perf_counter() - t0   # CPU port, one tell
+    cpu_tell, err0 = None, None
+    if cpu_tell_baseline:
+        opt = O.Cma(m0, 2.0, lam)
+        t0 = time.perf_counter(); opt.tell(X, f); cpu_tell = time.perf_counter() - t0   # CPU port, one tell
     ctx.cmaes_tell(X, f)
-    err0 = float(np.max(np.abs(ctx.cmaes_state()["C"] - opt.state()[2])) / np.max(np.abs(opt.state()[2])))
+    if cpu_tell_baseline:
+        err0 = float(np.max(np.abs(ctx.cmaes_state()["C"] - opt.state()[2])) / np.max(np.abs(opt.state()[2])))
     for _ in range(max(0, args.warmup - 1)):
         X = ctx.cmaes_ask(lam, rng.normal(size=(lam, n))); ctx.cmaes_tell(X, fobj(X))
     ctx.profile(True)
@@ -202,7 +212,7 @@ def cmaes(args):
     flop_gemm = 2.0 * n * n * lam * 3 + 2.0 * n * n * n * 3
     dfma = ctx.peak(2)
     a = flop_gemm / 2 / (max(gemm_ms, 1e-6) * 1e-3) / 1e9
-    print(json.dumps({
+    out = ({
         "metric": "cmaes_generations_per_s", "value": 1.0 / per_gen, "unit": "generations/s (ask+tell, n=512, popsize=4096)", "n_gpus": 1,
         "steps": gens, "warmup": args.warmup, "ms_per_step": per_gen * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -215,9 +225,13 @@ def cmaes(args):
         "roofline": {"bound": "fp64", "achieved": a, "peak": dfma, "unit": "GFMA/s FP64 on the GEMM part (DMMA)", "frac": a / dfma, "traffic": None,
                      "kernel": "dgemm_nt_kernel", "eigh_ms_per_generation": eig_ms, "ask_kernel_ms": prof[7][0] / gens, "tell_kernel_ms": prof[8][0] / gens,
                      "peak_source": "kb_peak_measure FP64 DFMA micro-kernel, this GPU, this run (of measured)"},
-        "cpu_baseline": {"value": 1.0 / cpu_tell, "unit": "generations/s (tell only)", "cores": 1, "kind": "port",
-                         "sample": f"one Tell at n=512, popsize=4096, {cpu_tell:.1f} s, oracle/cmaes.c (cyclic Jacobi + triple loops)"}}))
+        "cpu_baseline": None if cpu_tell is None else
+                        {"value": 1.0 / cpu_tell, "unit": "generations/s (tell only)", "cores": 1, "kind": "port",
+                         "sample": f"one Tell at n=512, popsize=4096, {cpu_tell:.1f} s, oracle/cmaes.c (cyclic Jacobi + triple loops)"}})
     ctx.close()
+    if emit:
+        print(json.dumps(out))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ configs[0]
@@ -290,6 +304,39 @@ def tpe3(args, calls=1000, device=0, emit=True):
     ctx.close()
     if emit:
         print(json.dumps(out))
+    return out
+
+
+def secondary_block(args, device=0):
+    """BASELINE configs[1], [2], [3] for the headline line's `secondary` object: the same measurements as
+    `bench.py --workload sobol|tpe20|cmaes`, a few steps each, reduced to the figures that matter."""
+    import types
+    a = types.SimpleNamespace(steps=3, warmup=3, cand=26)
+    out = {}
+    try:
+        r = sobol(a, device, emit=False)
+        out["sobol_2^24x64"] = {"baseline_config": "configs[1]", "points_per_s": r["value"], "ms_per_fill": r["ms_per_step"],
+                                "hbm_write_gbs": r["roofline"]["achieved"], "frac_of_measured_hbm": r["roofline"]["frac"],
+                                "bit_exact_vs_oracle": r["bit_exact_vs_oracle"], "e2e_points_per_s": r["e2e"]["value"],
+                                "cpu_port_points_per_s_1core": r["cpu_baseline"]["value"]}
+    except Exception as ex:  # a secondary figure must not take the headline line down
+        out["sobol_2^24x64"] = {"error": str(ex)[:200]}
+    try:
+        r = tpe20(a, device, emit=False)
+        out["tpe20_1k_1M"] = {"baseline_config": "configs[2]", "candidates_per_s": r["value"], "ms_per_step": r["ms_per_step"],
+                              "frac_of_measured_mufu": r["roofline"]["frac"], "e2e_candidates_per_s": r["e2e"]["value"],
+                              "winners_identical_on_4096_prefix": r["winners_identical_on_4096_prefix"],
+                              "cpu_port_candidates_per_s_1core": r["cpu_baseline"]["value"]}
+    except Exception as ex:
+        out["tpe20_1k_1M"] = {"error": str(ex)[:200]}
+    try:
+        a.steps = 20
+        r = cmaes(a, device, emit=False, cpu_tell_baseline=False)
+        out["cmaes_512x4096"] = {"baseline_config": "configs[3]", "generations_per_s": r["value"], "ms_per_generation": r["ms_per_step"],
+                                 "eigh_ms": r["roofline"]["eigh_ms_per_generation"], "dgemm_ms": r["dgemm_ms_per_generation"],
+                                 "dmma_frac_of_measured_dfma": r["roofline"]["frac"], "generations_timed": r["steps"]}
+    except Exception as ex:
+        out["cmaes_512x4096"] = {"error": str(ex)[:200]}
     return out
 
 
