@@ -225,6 +225,62 @@ __device__ __forceinline__ void two_sum_acc(float &hi, float &lo, float a) {
     hi = s;
 }
 
+// 2^e for e <= 0 on the FMA pipe (no MUFU): clamp, split e = n + f with the 1.5 * 2^23 rounding constant (n = round(e),
+// |f| <= 1/2), degree-5 polynomial for 2^f (2.0e-7 relative in FP32 -- the accuracy of MUFU.EX2 itself), n added into
+// the exponent field.  Packed FP32x2: 3 FADD2 + 5 FFMA2 per candidate pair; the clamp and the exponent insert run on
+// the ALU pipe.  e = -inf (padding entries) gives 2^-127 * (1 + 1e-7): a denormal, i.e. nothing.
+__device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
+    const float2 em = make_float2(fmaxf(e.x, -127.f), fmaxf(e.y, -127.f));
+    const float2 xm = __fadd2_rn(em, make_float2(12582912.f, 12582912.f));
+    const float2 nf = __fadd2_rn(xm, make_float2(-12582912.f, -12582912.f));
+    const float2 f = __ffma2_rn(nf, make_float2(-1.f, -1.f), em);
+    float2 p = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f,
+                          make_float2(9.675574488937855e-3f, 9.675574488937855e-3f));
+    p = __ffma2_rn(p, f, make_float2(5.550701171159744e-2f, 5.550701171159744e-2f));
+    p = __ffma2_rn(p, f, make_float2(2.4022118747234344e-1f, 2.4022118747234344e-1f));
+    p = __ffma2_rn(p, f, make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
+    p = __ffma2_rn(p, f, make_float2(1.0000001192092896f, 1.0000001192092896f));
+    return make_float2(__int_as_float(__float_as_int(p.x) + (__float_as_int(xm.x) << 23)),
+                       __int_as_float(__float_as_int(p.y) + (__float_as_int(xm.y) << 23)));
+}
+
+// One group of SC_GROUP (32) components applied to the SC_R candidates of a thread.  The MUFU pipe is the wall of this
+// loop (16 ex2 / clk / SM against 128 FP32 lanes): of every 16 components, those whose bit is set in SC_SW_MASK take
+// their 2^e from kb_ex2_fma2 instead, which moves that share of the exponentials onto the otherwise half-idle FMA
+// pipe.  Every (candidate, component) pair is still evaluated.
+// Masks for 0, 2, 3 and 4 of every 16 components; 3/16 balances the two pipes on paper (XU 13 cycles, FMA 13 cycles per
+// pair-component); KB_CONT_SW = 0 | 2 | 3 | 4 picks another at run time (measurement only).
+#define SC_SW_MASK_0 0x0000u
+#define SC_SW_MASK_2 0x0404u
+#define SC_SW_MASK_3 0x1084u
+#define SC_SW_MASK_4 0x4444u
+#ifndef SC_SW_DEFAULT
+#define SC_SW_DEFAULT 3
+#endif
+template <unsigned SC_SW_MASK>
+__device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const float2 (&xh)[SC_R / 2],
+                                           const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
+#pragma unroll 1
+    for (int h = 0; h < SC_GROUP; h += 16) {
+#pragma unroll
+        for (int jj = 0; jj < 16; jj++) {
+            const float4 A = tab[2 * (h + jj)], B = tab[2 * (h + jj) + 1];  // two broadcast LDS.128
+            const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
+            const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) {
+                float2 u = __fadd2_rn(xh[p], nmu);
+                u = __fadd2_rn(u, xl[p]);
+                const float2 t = __ffma2_rn(u, cs, ms);
+                const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                const float2 v = ((SC_SW_MASK >> jj) & 1u) ? kb_ex2_fma2(e) : make_float2(kb_ex2(e.x), kb_ex2(e.y));
+                a32[p] = __fadd2_rn(a32[p], v);
+            }
+        }
+    }
+}
+
+template <unsigned SW_MASK>
 __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                       const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
@@ -270,20 +326,7 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
             float2 a32[SC_R / 2];
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-#pragma unroll 4
-            for (int j = 0; j < SC_GROUP; j++) {
-                const float4 A = tab[2 * (j0 + j)], B = tab[2 * (j0 + j) + 1];  // two broadcast LDS.128
-                const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
-                const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    float2 u = __fadd2_rn(xh[p], nmu);
-                    u = __fadd2_rn(u, xl[p]);
-                    const float2 t = __ffma2_rn(u, cs, ms);
-                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
-                }
-            }
+            cont_group<SW_MASK>(tab + 2 * j0, xh, xl, a32);
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
@@ -392,6 +435,7 @@ tpe_bucket_scatter_kernel(const float2 *__restrict__ stage, long long chunk_cap,
 
 struct PruneSeg { const float4 *p; int cnt; int c0; int nch; };  // table segment: entries (multiple of 32), first chunk, chunks
 
+template <unsigned SW_MASK>
 __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                              const float2 *__restrict__ sorted, const int32_t *__restrict__ perm, long long chunk_cap, int n,
@@ -482,20 +526,7 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
             float2 a32[SC_R / 2];
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-#pragma unroll 4
-            for (int j = 0; j < SC_GROUP; j++) {
-                const float4 A = tab[2 * (j0 + j)], B = tab[2 * (j0 + j) + 1];
-                const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
-                const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    float2 u = __fadd2_rn(xh[p], nmu);
-                    u = __fadd2_rn(u, xl[p]);
-                    const float2 t = __ffma2_rn(u, cs, ms);
-                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
-                }
-            }
+            cont_group<SW_MASK>(tab + 2 * j0, xh, xl, a32);
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
@@ -1154,15 +1185,23 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
                                                               ctx->d_stage_sorted, ctx->d_perm);
         KB_LAUNCH_CHECK(ctx);
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
-        tpe_score_cont_pruned_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
+        tpe_score_cont_pruned_kernel<SC_SW_MASK_3><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
                                                                  ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score,
                                                                  ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
     } else if (ctx->n_cont > 0) {
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
         KbProf pf(ctx, 1, s);
-        tpe_score_cont_kernel<<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont, ctx->chunk_cap, n,
-                                                          idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores);
+        static const int sw = [] { const char *e = getenv("KB_CONT_SW"); return e ? atoi(e) : SC_SW_DEFAULT; }();
+#define KB_CONT_LAUNCH(MASK)                                                                                              \
+        tpe_score_cont_kernel<MASK><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont,           \
+                                                                ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,           \
+                                                                sc->d_tie_score, ctx->tie_slots, d_cand, d_scores)
+        if (sw == 0) KB_CONT_LAUNCH(SC_SW_MASK_0);
+        else if (sw == 2) KB_CONT_LAUNCH(SC_SW_MASK_2);
+        else if (sw == 4) KB_CONT_LAUNCH(SC_SW_MASK_4);
+        else KB_CONT_LAUNCH(SC_SW_MASK_3);
+#undef KB_CONT_LAUNCH
         KB_LAUNCH_CHECK(ctx);
     }
     if (ctx->n_quant > 0) {
