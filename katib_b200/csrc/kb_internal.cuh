@@ -50,6 +50,14 @@ struct KbDim {
     // The component's second float4 then carries (grid index * 128 + 64) as an integer in .w (0 = not this class).
     float *lut[2];
     int32_t lut_G[2];         // 0: class switched off for this (parameter, side)
+    // The same components once more, laid out for the grid kernel (tpe_score_quant_grid_kernel): the look-up-class
+    // components' weights as a dense float array in table (mu-sorted) order, qw[side][Kn], cut into runs of equal grid
+    // point, qruns[side][n_runs] = {grid code, first index into qw, length, 0} -- a run's table value is fetched once
+    // per candidate and every component of it costs half a packed FFMA.  All other components (the prior, wide sigmas,
+    // anything off the grid) sit in tabw[side][Kw] in the usual two-float4 form.  Kn / Kw hold the two counts.
+    float *qw[2];
+    int4 *qruns[2];
+    int32_t n_runs[2];
     // continuous parameters, KB_OPT_PRUNE_FAR: the same table split into the components whose sigma sits on the
     // magic-clip floor ("narrow", still sorted by mu, Kn entries padded to KB_TABLE_PAD) and the rest ("wide", Kw
     // entries, padded).  A narrow component further than prune_w (normalised) from a candidate contributes less than
@@ -136,6 +144,7 @@ struct kb_ctx {
     double *d_cand_chunk[2] = {nullptr, nullptr};   // H2D landing buffers (row-major f64)
     float2 *d_stage_cont = nullptr;  // [n_cont][chunk]   (x_hi, x_lo) normalised
     float4 *d_stage_quant = nullptr; // [n_quant][chunk]  (lb_hi, lb_lo, ub_hi, ub_lo) normalised
+    int *d_qflags = nullptr;         // [n_quant][tiles]  1 = tile left to the general quantised kernel by the grid kernel
     double *d_scores_chunk = nullptr; // [chunk x D] dense scores (kb_tpe_scores only)
     KbSelect *d_sel = nullptr;       // [D]
     KbTie *d_tie = nullptr;          // [n_numeric][tie_slots]

@@ -370,6 +370,57 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
         tab[2 * j] = A;
         tab[2 * j + 1] = B;
     }
+    // Quantised parameters: split the entries, in order, into the look-up class (grid code != 0: dense weights + run
+    // table, see KbDim::qw) and the rest (tabw).  A stable partition by a block scan over per-thread segments, then a
+    // second scan over the look-up-class entries that numbers the runs of equal grid code.
+    if (quant) {
+        __syncthreads();
+        float *qw = dm.qw[side];
+        float4 *to = dm.tabw[side];
+        int4 *runs = dm.qruns[side];
+        const int seg = (K + nt - 1) / nt, b0 = min(K, tid * seg), b1 = min(K, b0 + seg);
+        int c = 0;
+        for (int j = b0; j < b1; j++) c += __float_as_int(tab[2 * j + 1].w) != 0 ? 1 : 0;
+        s_int[tid] = c;
+        __syncthreads();
+        for (int off = 1; off < nt; off <<= 1) {
+            int v = tid >= off ? s_int[tid - off] : 0;
+            __syncthreads();
+            s_int[tid] += v;
+            __syncthreads();
+        }
+        const int Kg = s_int[nt - 1], Ko = K - Kg;
+        int bg = s_int[tid] - c, bo = b0 - bg;
+        __syncthreads();
+        for (int j = b0; j < b1; j++) {
+            const float4 Bj = tab[2 * j + 1];
+            const int code = __float_as_int(Bj.w);
+            if (code != 0) { qw[bg] = fabsf(Bj.z); idx[bg] = (uint32_t)code; bg++; }
+            else { to[2 * bo] = tab[2 * j]; to[2 * bo + 1] = Bj; bo++; }
+        }
+        const float4 Z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = Kg + tid; j < (Kg + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) qw[j] = 0.f;
+        for (int j = Ko + tid; j < (Ko + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { to[2 * j] = Z; to[2 * j + 1] = Z; }
+        __syncthreads();
+        const int seg2 = (Kg + nt - 1) / nt, g0 = min(Kg, tid * seg2), g1 = min(Kg, g0 + seg2);
+        int h = 0;
+        for (int p = g0; p < g1; p++) h += (p == 0 || idx[p] != idx[p - 1]) ? 1 : 0;
+        s_int[tid] = h;
+        __syncthreads();
+        for (int off = 1; off < nt; off <<= 1) {
+            int v = tid >= off ? s_int[tid - off] : 0;
+            __syncthreads();
+            s_int[tid] += v;
+            __syncthreads();
+        }
+        const int n_runs = s_int[nt - 1];  // <= grid points <= KB_LUT_MAX / 2 (codes are non-decreasing in table order)
+        int r = s_int[tid] - h;
+        for (int p = g0; p < g1; p++)
+            if (p == 0 || idx[p] != idx[p - 1]) { runs[r] = make_int4((int)idx[p], p, 0, 0); r++; }
+        __syncthreads();
+        for (int q = tid; q < n_runs; q += nt) runs[q].z = (q + 1 < n_runs ? runs[q + 1].y : Kg) - runs[q].y;
+        if (tid == 0) { dm.Kn[side] = Kg; dm.Kw[side] = Ko; dm.n_runs[side] = n_runs; }
+    }
     // KB_OPT_PRUNE_FAR (continuous parameters): the same entries split, in order, into floor-sigma ("narrow") and
     // other ("wide") components -- see KbDim::tabn.  A stable partition by a block scan over per-thread segments.
     if (!quant) {
@@ -510,7 +561,8 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
     for (int d = 0; d < D; d++) {
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
-        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 6 * sizeof(float4)) + KB_LUT_MAX * sizeof(float));
+        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 6 * sizeof(float4)) + KB_LUT_MAX * sizeof(float) +
+                           (KB_LUT_MAX / 2) * sizeof(int4));
     }
     if (bytes > ctx->tabmem_bytes) {
         cudaFree(ctx->d_tabmem); ctx->d_tabmem = nullptr;
@@ -536,6 +588,8 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
                 k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.logc[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.lut[side] = (float *)p; p += KB_LUT_MAX * sizeof(float);
+                k.qruns[side] = (int4 *)p; p += (KB_LUT_MAX / 2) * sizeof(int4);
+                k.qw[side] = (float *)k.tabn[side];  // quantised parameters have no "narrow" table: the area holds qw
             }
         }
     }

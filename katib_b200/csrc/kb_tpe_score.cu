@@ -630,10 +630,13 @@ __global__ void __launch_bounds__(SC_THREADS, SQ_MINB)
 tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
                        const float4 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                        KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
-                       const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
+                       const double *__restrict__ cand_raw, double *__restrict__ scores_out,
+                       const int *__restrict__ tile_flags, int tiles_stride) {
     __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     extern __shared__ __align__(128) float s_lut[];  // [2G - 1][32]: the current side's look-up table, one copy per bank
+    // this tile was scored by tpe_score_quant_grid_kernel (all of its candidates on the grid): nothing left to do
+    if (tile_flags && tile_flags[blockIdx.y * tiles_stride + blockIdx.x] == 0) return;
     const int slot = blockIdx.y;
     const int d = quant_dims[slot];
     const KbDim &dm = dims[d];
@@ -840,6 +843,219 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
     }
     if (sel) select_publish<SQ_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
                                                   KB_MARGIN_QUANT, cand_raw);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// quantised parameters, the common case: every candidate of the tile sits ON the quantisation grid (what the sampler
+// produces) and the parameter has a look-up table.  Nearly all components are look-up-class then (observations of an
+// integer / stepped parameter are on the grid, and a dense history clips their sigma to the floor); the build kernel
+// has laid them out as a dense weight array cut into runs of equal grid point (KbDim::qw / qruns).  Per run the table
+// value of each candidate is fetched once (one conflict-free LDS from the bank-replicated table), then every
+// component of the run is one broadcast weight (LDS.128 per four components) and one packed FFMA per candidate pair:
+// the FP32 FMA pipe is the bound, no shuffles, ballots or class branches in the loop.  Every (candidate, component)
+// pair is visited.  The few other components (prior, wide sigmas) come from KbDim::tabw and take the arithmetic
+// classes.  A tile with an off-grid candidate, or a parameter without a table, is flagged instead and left to
+// tpe_score_quant_kernel, which runs right after this kernel and skips the tiles done here.
+// ---------------------------------------------------------------------------------------------------------
+#define SQG_R 8
+#define SQG_WCHUNK 4096     // weights per shared-memory stage (16 KB), two stages
+#ifndef SQG_FLUSH
+#define SQG_FLUSH 128       // components per FP32 partial sum before it is folded into the (hi, lo) pair
+#endif
+#define SQG_OTHER 64        // other-class entries per shared-memory pass
+static_assert(SQG_R == SQ_R, "the grid kernel and tpe_score_quant_kernel must agree on the tile size");
+
+__global__ void __launch_bounds__(SC_THREADS, 3)
+tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
+                            const float4 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
+                            KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
+                            const double *__restrict__ cand_raw, double *__restrict__ scores_out, int *tile_flags,
+                            int tiles_stride) {
+    __shared__ __align__(128) float s_w[2][SQG_WCHUNK];
+    __shared__ __align__(16) float4 s_other[SQG_OTHER * 2];
+    __shared__ int4 s_runs[KB_LUT_MAX / 2];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    extern __shared__ __align__(128) float s_lut[];  // [2G - 1][32]: the current side's look-up table, one copy per bank
+    const int slot = blockIdx.y;
+    const int d = quant_dims[slot];
+    const KbDim &dm = dims[d];
+    const int tile_base = blockIdx.x * SQ_TILE;
+    const int G = dm.lut_G[0];
+    const float4 *my_stage = stage + (size_t)slot * chunk_cap;
+
+    uint32_t xo[SQG_R];  // byte offset of this lane's copy of table row (grid index + G - 1), + 64 (see KbDim::lut)
+    bool all_grid = G > 0 && dm.lut_G[1] == G;
+    const uint32_t lut_lane = ((threadIdx.x & 31u) << 2) + 64u;
+#pragma unroll
+    for (int r = 0; r < SQG_R; r++) {
+        const int i = tile_base + r * SC_THREADS + threadIdx.x;
+        const float code = i < n ? my_stage[i].w : 2.f;
+        const int gi = (int)code - 2;
+        all_grid = all_grid && gi >= 0 && gi < G;
+        xo[r] = lut_lane + ((uint32_t)(gi + G - 1) << 7);
+    }
+    const int ok = __syncthreads_and(all_grid ? 1 : 0);
+    if (threadIdx.x == 0) {
+        tile_flags[slot * tiles_stride + blockIdx.x] = ok ? 0 : 1;
+        if (ok) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); mbar_fence_init(); }
+    }
+    if (!ok) return;
+    __syncthreads();
+
+    float Shi[SQG_R], Slo[SQG_R];
+    float2 a32[SQG_R / 2], tvp[SQG_R / 2];
+    double P0[SQG_R];
+    int it = 0;  // weight stages consumed so far (both sides): stage = it & 1, mbarrier parity = (it >> 1) & 1
+    for (int side = 0; side < 2; side++) {
+        const int Kg = dm.Kn[side], Ko = dm.Kw[side], nr = dm.n_runs[side];
+        const float *qw = dm.qw[side];
+        const int nst = (Kg + SQG_WCHUNK - 1) / SQG_WCHUNK;
+        // the side's look-up table (one copy per bank) and run table; every thread is past the previous side's loops
+        const int rows = 2 * G - 1;
+        for (int e = threadIdx.x; e < rows * 32; e += SC_THREADS) s_lut[e] = dm.lut[side][e >> 5];
+        for (int e = threadIdx.x; e < nr; e += SC_THREADS) s_runs[e] = dm.qruns[side][e];
+        if (threadIdx.x == 0)
+            for (int c = 0; c < 2 && c < nst; c++) {
+                const uint32_t bytes = (uint32_t)((min(SQG_WCHUNK, Kg - c * SQG_WCHUNK) + 3) & ~3) * 4u;  // qw is zero-padded
+                mbar_expect_tx(&s_bar[(it + c) & 1], bytes);
+                tma_bulk_g2s(s_w[(it + c) & 1], qw + (size_t)c * SQG_WCHUNK, bytes, &s_bar[(it + c) & 1]);
+            }
+#pragma unroll
+        for (int r = 0; r < SQG_R; r++) { Shi[r] = 0.f; Slo[r] = 0.f; }
+#pragma unroll
+        for (int p = 0; p < SQG_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
+        auto flush = [&]() {
+#pragma unroll
+            for (int p = 0; p < SQG_R / 2; p++) {
+                two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
+                two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
+                a32[p] = make_float2(0.f, 0.f);
+            }
+        };
+        // ---- the other components (arithmetic classes), while the first weight stages are in flight
+        {
+            float xm[SQG_R], xl[SQG_R], hw[SQG_R];
+#pragma unroll
+            for (int r = 0; r < SQG_R; r++) {
+                const int i = tile_base + r * SC_THREADS + threadIdx.x;
+                const float4 v = i < n ? my_stage[i] : make_float4(0.5f, 0.f, dm.qf_hw[0], 2.f);
+                xm[r] = v.x; xl[r] = v.y; hw[r] = v.z;
+            }
+            const float qn = (float)(dm.q / (dm.hi - dm.lo));
+            const int Kop = (Ko + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
+            for (int o0 = 0; o0 < Kop; o0 += SQG_OTHER) {
+                const int cnt = min(SQG_OTHER, Kop - o0);
+                __syncthreads();
+                for (int e = threadIdx.x; e < cnt * 2; e += SC_THREADS) s_other[e] = dm.tabw[side][(size_t)o0 * 2 + e];
+                __syncthreads();
+                for (int j = 0; j < cnt; j++) {
+                    const float4 A = s_other[2 * j], B = s_other[2 * j + 1];
+                    const float wj = fabsf(B.z);
+                    if (wj == 0.f) continue;  // padding
+                    if (A.z * qn < QUANT_WIDE_THR) {  // narrow bin: series about the midpoint
+#pragma unroll
+                        for (int r = 0; r < SQG_R; r++) {
+                            const float m = fmaf((xm[r] + A.x) + xl[r], A.z, B.x), h = hw[r] * A.z;
+                            const float mm = m * m;
+                            const float u = mm * LN2F, v = (h * h) * LN2F;
+                            const float c1 = fmaf(u, 0.6666666667f, -0.3333333333f);
+                            const float c2 = fmaf(fmaf(u, 0.1333333333f, -0.4f), u, 0.1f);
+                            const float c3 = fmaf(fmaf(fmaf(u, 0.0126984127f, -0.0952380952f), u, 0.1428571429f), u, -0.0238095238f);
+                            const float S = fmaf(fmaf(fmaf(c3, v, c2), v, c1), v, 1.0f);
+                            const float d2 = (h * (2.2567583342f * KINVF)) * S * kb_ex2(-mm);
+                            if (r & 1) a32[r / 2].y = fmaf(wj, d2, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, d2, a32[r / 2].x);
+                        }
+                    } else {  // erfc(a) - erfc(b), mirrored so that b >= |a|
+#pragma unroll
+                        for (int r = 0; r < SQG_R; r++) {
+                            const float ma = fabsf(fmaf((xm[r] + A.x) + xl[r], A.z, B.x)), h = hw[r] * A.z;
+                            const float a2 = ma - h, b2 = ma + h;
+                            const float ea = erfc_pos_scaled(fabsf(a2)), eb = erfc_pos_scaled(b2);
+                            const float ea2 = a2 < 0.f ? 2.0f - ea : ea;
+                            if (r & 1) a32[r / 2].y = fmaf(wj, ea2 - eb, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, ea2 - eb, a32[r / 2].x);
+                        }
+                    }
+                }
+                flush();
+            }
+        }
+        __syncthreads();  // s_lut and s_runs are complete (the loop above may have run zero times)
+        // ---- the look-up-class components, run by run
+        int ri = 0, since = 0;
+        for (int c = 0; c < nst; c++, it++) {
+            const int st = it & 1;
+            mbar_wait(&s_bar[st], (uint32_t)((it >> 1) & 1));
+            const float *w = s_w[st];
+            const int base = c * SQG_WCHUNK, cnt = min(SQG_WCHUNK, Kg - base);
+            while (ri < nr) {
+                const int4 run = s_runs[ri];
+                if (run.y >= base + cnt) break;
+                const int a = max(run.y, base) - base, b = min(run.y + run.z, base + cnt) - base;
+#pragma unroll
+                for (int r = 0; r < SQG_R; r++) {
+                    const float tv = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(s_lut) + (xo[r] - (uint32_t)run.x));
+                    if (r & 1) tvp[r / 2].y = tv; else tvp[r / 2].x = tv;
+                }
+                int j = a;
+                while (j < b) {
+                    const int m = min(b - j, SQG_FLUSH - since);
+                    const float *wp = w + j;
+                    int k = 0;
+                    const int head = min(m, (4 - (j & 3)) & 3);
+                    for (; k < head; k++) {
+                        const float2 w2 = make_float2(wp[k], wp[k]);
+#pragma unroll
+                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(w2, tvp[p], a32[p]);
+                    }
+#pragma unroll 2
+                    for (; k + 4 <= m; k += 4) {
+                        const float4 w4 = *reinterpret_cast<const float4 *>(wp + k);  // one broadcast LDS.128: four weights
+                        const float2 wa = make_float2(w4.x, w4.x), wb = make_float2(w4.y, w4.y);
+                        const float2 wc = make_float2(w4.z, w4.z), wd = make_float2(w4.w, w4.w);
+#pragma unroll
+                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(wa, tvp[p], a32[p]);
+#pragma unroll
+                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(wb, tvp[p], a32[p]);
+#pragma unroll
+                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(wc, tvp[p], a32[p]);
+#pragma unroll
+                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(wd, tvp[p], a32[p]);
+                    }
+                    for (; k < m; k++) {
+                        const float2 w2 = make_float2(wp[k], wp[k]);
+#pragma unroll
+                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(w2, tvp[p], a32[p]);
+                    }
+                    j += m; since += m;
+                    if (since >= SQG_FLUSH) { flush(); since = 0; }
+                }
+                if (run.y + run.z <= base + cnt) ri++; else break;
+            }
+            __syncthreads();  // every thread is done with stage st
+            if (threadIdx.x == 0 && c + 2 < nst) {
+                const uint32_t bytes = (uint32_t)((min(SQG_WCHUNK, Kg - (c + 2) * SQG_WCHUNK) + 3) & ~3) * 4u;
+                mbar_expect_tx(&s_bar[st], bytes);
+                tma_bulk_g2s(s_w[st], qw + (size_t)(c + 2) * SQG_WCHUNK, bytes, &s_bar[st]);
+            }
+        }
+        flush();
+        if (side == 0) {
+#pragma unroll
+            for (int r = 0; r < SQG_R; r++)
+                P0[r] = log(0.5 * ((double)Shi[r] + (double)Slo[r]) + KB_EPS) - log(dm.p_accept[0] + KB_EPS);
+        }
+        __syncthreads();  // the next side overwrites s_lut / s_runs
+    }
+    float sc[SQG_R];
+#pragma unroll
+    for (int r = 0; r < SQG_R; r++) {
+        const double s64 = P0[r] - (log(0.5 * ((double)Shi[r] + (double)Slo[r]) + KB_EPS) - log(dm.p_accept[1] + KB_EPS));
+        sc[r] = (float)s64;
+        const int i = tile_base + r * SC_THREADS + threadIdx.x;
+        if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
+    }
+    if (sel) select_publish<SQG_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
+                                                   KB_MARGIN_QUANT, cand_raw);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1087,6 +1303,7 @@ int kb_tpe_free(kb_ctx *ctx) {
     ctx->chunk_cap = 0;
     cudaFree(ctx->d_stage_sorted); cudaFree(ctx->d_perm); cudaFree(ctx->d_bucket);
     ctx->d_stage_sorted = nullptr; ctx->d_perm = nullptr; ctx->d_bucket = nullptr;
+    cudaFree(ctx->d_qflags); ctx->d_qflags = nullptr;
     cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
     cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list); cudaFree(ctx->d_tie_count); cudaFree(ctx->d_slot_of_dim); cudaFree(ctx->d_numeric_dims);
     if (ctx->h_win) cudaFreeHost(ctx->h_win);
@@ -1148,6 +1365,8 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
         ctx->chunk_cap = 0;
         KB_CUDA(ctx, cudaMalloc(&ctx->d_stage_cont, sizeof(float2) * (size_t)rows * (size_t)(ctx->n_cont > 0 ? ctx->n_cont : 1)));
         KB_CUDA(ctx, cudaMalloc(&ctx->d_stage_quant, sizeof(float4) * (size_t)rows * (size_t)(ctx->n_quant > 0 ? ctx->n_quant : 1)));
+        cudaFree(ctx->d_qflags); ctx->d_qflags = nullptr;
+        KB_CUDA(ctx, cudaMalloc(&ctx->d_qflags, sizeof(int) * (size_t)((rows + SQ_TILE - 1) / SQ_TILE) * (size_t)(ctx->n_quant > 0 ? ctx->n_quant : 1)));
         ctx->chunk_cap = rows;
     }
     if (need_landing && !ctx->d_cand_chunk[0])
@@ -1210,10 +1429,23 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
         const size_t lut_bytes = (size_t)KB_LUT_MAX * 32 * sizeof(float);  // bank-replicated look-up table
         if (!ctx->quant_attr_set) {  // once per context (static 32 KB + dynamic 32 KB > the 48 KB default)
             KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lut_bytes));
+            KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_quant_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lut_bytes));
             ctx->quant_attr_set = true;
         }
+        // on-grid tiles (the rule) in the grid kernel; it flags the others for the general kernel.  KB_QUANT_GRID=0
+        // sends everything through the general kernel (measurement only)
+        static const bool use_grid = [] { const char *e = getenv("KB_QUANT_GRID"); return !(e && e[0] == '0'); }();
+        const int tiles_stride = (int)((ctx->chunk_cap + SQ_TILE - 1) / SQ_TILE);
+        if (use_grid) {
+            tpe_score_quant_grid_kernel<<<grid, SC_THREADS, lut_bytes, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant,
+                                                                            ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,
+                                                                            sc->d_tie_score, ctx->tie_slots, d_cand, d_scores,
+                                                                            ctx->d_qflags, tiles_stride);
+            KB_LAUNCH_CHECK(ctx);
+        }
         tpe_score_quant_kernel<<<grid, SC_THREADS, lut_bytes, s>>>(ctx->d_dims, ctx->d_quant_dims, ctx->d_stage_quant, ctx->chunk_cap,
-                                                           n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores);
+                                                           n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores,
+                                                           use_grid ? ctx->d_qflags : nullptr, tiles_stride);
         KB_LAUNCH_CHECK(ctx);
     }
     return KB_OK;
