@@ -251,11 +251,12 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
 // Masks for 0, 2, 3 and 4 of every 16 components; 3/16 balances the two pipes on paper (XU 13 cycles, FMA 13 cycles per
 // pair-component); KB_CONT_SW = 0 | 2 | 3 | 4 picks another at run time (measurement only).
 #define SC_SW_MASK_0 0x0000u
+#define SC_SW_MASK_1 0x0100u
 #define SC_SW_MASK_2 0x0404u
 #define SC_SW_MASK_3 0x1084u
 #define SC_SW_MASK_4 0x4444u
 #ifndef SC_SW_DEFAULT
-#define SC_SW_DEFAULT 3
+#define SC_SW_DEFAULT 0
 #endif
 template <unsigned SC_SW_MASK>
 __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const float2 (&xh)[SC_R / 2],
@@ -267,14 +268,50 @@ __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const
             const float4 A = tab[2 * (h + jj)], B = tab[2 * (h + jj) + 1];  // two broadcast LDS.128
             const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
             const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
+            if ((SC_SW_MASK >> jj) & 1u) {
+                // the four candidate pairs go through the polynomial in lockstep (independent chains back to back)
+                float2 em[SC_R / 2], xm[SC_R / 2], f[SC_R / 2], q[SC_R / 2];
 #pragma unroll
-            for (int p = 0; p < SC_R / 2; p++) {
-                float2 u = __fadd2_rn(xh[p], nmu);
-                u = __fadd2_rn(u, xl[p]);
-                const float2 t = __ffma2_rn(u, cs, ms);
-                const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                const float2 v = ((SC_SW_MASK >> jj) & 1u) ? kb_ex2_fma2(e) : make_float2(kb_ex2(e.x), kb_ex2(e.y));
-                a32[p] = __fadd2_rn(a32[p], v);
+                for (int p = 0; p < SC_R / 2; p++) {
+                    float2 u = __fadd2_rn(xh[p], nmu);
+                    u = __fadd2_rn(u, xl[p]);
+                    const float2 t = __ffma2_rn(u, cs, ms);
+                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                    em[p] = make_float2(fmaxf(e.x, -127.f), fmaxf(e.y, -127.f));
+                }
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) xm[p] = __fadd2_rn(em[p], make_float2(12582912.f, 12582912.f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) f[p] = __fadd2_rn(xm[p], make_float2(-12582912.f, -12582912.f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) f[p] = __ffma2_rn(f[p], make_float2(-1.f, -1.f), em[p]);
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++)
+                    q[p] = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f[p],
+                                      make_float2(9.675574488937855e-3f, 9.675574488937855e-3f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(5.550701171159744e-2f, 5.550701171159744e-2f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(2.4022118747234344e-1f, 2.4022118747234344e-1f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(1.0000001192092896f, 1.0000001192092896f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) {
+                    const float2 v = make_float2(__int_as_float(__float_as_int(q[p].x) + (__float_as_int(xm[p].x) << 23)),
+                                                 __int_as_float(__float_as_int(q[p].y) + (__float_as_int(xm[p].y) << 23)));
+                    a32[p] = __fadd2_rn(a32[p], v);
+                }
+            } else {
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) {
+                    float2 u = __fadd2_rn(xh[p], nmu);
+                    u = __fadd2_rn(u, xl[p]);
+                    const float2 t = __ffma2_rn(u, cs, ms);
+                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
+                }
             }
         }
     }
@@ -1417,6 +1454,7 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long 
                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,           \
                                                                 sc->d_tie_score, ctx->tie_slots, d_cand, d_scores)
         if (sw == 0) KB_CONT_LAUNCH(SC_SW_MASK_0);
+        else if (sw == 1) KB_CONT_LAUNCH(SC_SW_MASK_1);
         else if (sw == 2) KB_CONT_LAUNCH(SC_SW_MASK_2);
         else if (sw == 4) KB_CONT_LAUNCH(SC_SW_MASK_4);
         else KB_CONT_LAUNCH(SC_SW_MASK_3);
