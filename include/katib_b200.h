@@ -153,7 +153,13 @@ int kb_tpe_scores_noalloc(int device, int64_t n_cand, const double *cand_device,
 
 /* Full tpe.Sampler.Sample for every parameter (sample.go:48-90): draw n_ei_candidates from l(x)
  * on the device (Philox4x32-10 keyed by seed; goptuna's math/rand stream is not reproducible),
- * score, select.  out_value[n_params] in internal representation. */
+ * score, select.  out_value[n_params] in internal representation.  The candidates are the ones
+ * kb_tpe_sample_candidates returns for the same seed, but they are never stored: each chunk is drawn
+ * straight into the scoring kernels' staging columns, so the scratch does not grow with
+ * n_ei_candidates.  With a communicator (kb_comm_init) and n_ei_candidates >= 65536 every rank must
+ * call with the same arguments: rank r draws and scores only its contiguous index range of the one
+ * stream, one collective merges the winners and every rank returns the unsharded call's values.
+ * Below 65536 candidates there is no collective and a rank may call alone. */
 int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t seed, double *out_value);
 /* Draw only (sampleFromGMM / sampleFromCategoricalDist): cand[n x n_params] row-major, working
  * domain.  cand_device may be NULL when cand_host is given and vice versa. */
@@ -219,6 +225,14 @@ int kb_random_fill(kb_ctx *ctx, uint64_t seed, uint64_t first_index, int64_t n, 
  * experiment, like one reference service process per Suggestion CR (composer.go:72-146). */
 typedef struct kb_service kb_service;
 int kb_service_create(int device, kb_service **out);
+/* The same service over several GPUs of this machine (devices[0 .. n_devices), distinct).  The controller talks to ONE
+ * service process per experiment (composer.go:72-146; main.go:43-57), so the GPUs are driven from inside it: one
+ * kb_ctx and one host thread per GPU, one NCCL communicator owned by the service.  Requests are answered by devices[0]
+ * alone, except TPE requests whose n_ei_candidates setting is at least 65536: then every GPU draws and scores its
+ * contiguous index range of the candidate stream and one collective per suggestion merges the winners -- the reply is
+ * the one a single-GPU service gives for the same request.  Contexts and communicator are made at the first
+ * GetSuggestions, like the reference's study (service.go:153-171). */
+int kb_service_create_multi(int n_devices, const int *devices, kb_service **out);
 int kb_service_destroy(kb_service *svc);
 /* SuggestionService.GetSuggestions (service.go:54-93).  *reply points into memory owned by svc, valid until the
  * next call on it. */

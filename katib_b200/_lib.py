@@ -86,6 +86,7 @@ def lib():
         "kb_launch_count": ([vp], i64),
         "kb_tpe_scores_noalloc": ([i32, i64, vp, i32, vp, vp, vp, i32, vp, vp, vp, dbl, dbl, vp, vp], i32),
         "kb_service_create": ([i32, C.POINTER(vp)], i32),
+        "kb_service_create_multi": ([i32, C.POINTER(i32), C.POINTER(vp)], i32),
         "kb_service_destroy": ([vp], i32),
         "kb_service_get_suggestions": ([vp, vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_size_t)], i32),
         "kb_service_validate_algorithm_settings": ([vp, vp, C.c_size_t], i32),
@@ -122,11 +123,16 @@ class Service:
     """kb_service: the suggestion service above the kernels.  Requests / replies are serialized protobuf bytes."""
     OK, INVALID_ARGUMENT, INTERNAL = 0, 3, 13
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, devices=None):
+        """devices: a list of CUDA device indices -> kb_service_create_multi (one service over several GPUs)"""
         self._h = C.c_void_p()
-        rc = lib().kb_service_create(device, C.byref(self._h))
+        if devices is not None and len(devices) > 1:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = lib().kb_service_create_multi(len(devices), arr, C.byref(self._h))
+        else:
+            rc = lib().kb_service_create(devices[0] if devices else device, C.byref(self._h))
         if rc:
-            raise KbError(rc, "kb_service_create failed")
+            raise KbError(rc, "kb_service_create failed: " + lib().kb_last_error(None).decode())
 
     def close(self):
         if getattr(self, "_h", None):

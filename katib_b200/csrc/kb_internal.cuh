@@ -158,8 +158,6 @@ struct kb_ctx {
     int *d_slot_of_dim = nullptr;    // [D] index of a parameter inside its cont / quant / cat list
     int *d_numeric_dims = nullptr;   // [n_numeric] parameter index per numeric slot
     KbWinner *h_win = nullptr;       // pinned host mirror of d_win
-    double *d_suggest = nullptr;     // candidates drawn by kb_tpe_suggest (grow-only)
-    int64_t suggest_cap = 0;
     cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
     cudaEvent_t ev_build = nullptr;  // recorded on `stream` after every history build; caller streams wait on it
 

@@ -21,11 +21,13 @@
 #include <cstdlib>
 #include <map>
 #include <set>
+#include <thread>
 #include <unordered_set>
 
 #include "kb_internal.cuh"
 
 enum { GRPC_OK = 0, GRPC_INVALID_ARGUMENT = 3, GRPC_INTERNAL = 13 };
+#define KB_SERVICE_SHARD_MIN 65536  // = KB_SUGGEST_SHARD_MIN of kb_tpe_suggest: from here on n_ei_candidates is sharded
 
 // ---------------------------------------------------------------------------------------------------------------
 // minimal protobuf wire reader / writer (varint, 64-bit, length-delimited, 32-bit)
@@ -281,6 +283,11 @@ struct kb_service {
     std::mutex mu;
     int device = 0;
     kb_ctx *ctx = nullptr;
+    // kb_service_create_multi: the other GPUs of this service.  ctx (on devices[0]) is rank 0 of one NCCL communicator
+    // over all of them and the only context that serves CMA-ES, Sobol, random and small TPE requests; the peers hold
+    // replicas of the search space and the TPE history and join in when a TPE request is large enough to shard.
+    std::vector<int> devices;
+    std::vector<kb_ctx *> peers;  // ranks 1 .. n-1
     bool initialised = false;
     Algo algo;
     std::vector<Param> space;
@@ -488,6 +495,21 @@ static Status engine_error(kb_service *s, const char *what) {
     return fail(GRPC_INTERNAL, std::string(what) + ": " + kb_last_error(s->ctx));
 }
 
+// f(rank, ctx) on every context of the service, one host thread per GPU: calls that contain a collective block until
+// all ranks have entered it.  Returns the first non-zero code (and that context, for its error text).
+template <class F>
+static int on_all_contexts(kb_service *s, F f, kb_ctx **failed = nullptr) {
+    const size_t n = 1 + s->peers.size();
+    std::vector<int> rc(n, 0);
+    std::vector<std::thread> th;
+    for (size_t r = 1; r < n; r++) th.emplace_back([&, r] { rc[r] = f((int)r, s->peers[r - 1]); });
+    rc[0] = f(0, s->ctx);
+    for (auto &t : th) t.join();
+    for (size_t r = 0; r < n; r++)
+        if (rc[r]) { if (failed) *failed = r == 0 ? s->ctx : s->peers[r - 1]; return rc[r]; }
+    return 0;
+}
+
 // upload Complete (and value-less Pruned, ranked last) trials as the TPE history
 static Status PushHistory(kb_service *s) {
     if (!s->history_dirty) return Status();
@@ -510,10 +532,14 @@ static Status PushHistory(kb_service *s) {
         for (const Param &p : s->space) values.push_back(t.params.at(p.name));
         loss.push_back(t.state == ST_COMPLETE ? (s->maximize ? -t.value : t.value) : INFINITY);
     }
-    const int rc = keep > 0
-        ? kb_tpe_append_history(s->ctx, (int64_t)loss.size(), values.empty() ? nullptr : values.data(), loss.empty() ? nullptr : loss.data())
-        : kb_tpe_set_history(s->ctx, (int64_t)loss.size(), values.empty() ? nullptr : values.data(), loss.empty() ? nullptr : loss.data());
-    if (rc) { s->uploaded.clear(); return engine_error(s, keep > 0 ? "kb_tpe_append_history" : "kb_tpe_set_history"); }
+    // every GPU of the service builds the same tables from the same rows (no exchange: the build is deterministic)
+    const double *vp = values.empty() ? nullptr : values.data(), *lp = loss.empty() ? nullptr : loss.data();
+    int rc = 0;
+    for (size_t r = 0; r <= s->peers.size() && !rc; r++) {
+        kb_ctx *c = r == 0 ? s->ctx : s->peers[r - 1];
+        rc = keep > 0 ? kb_tpe_append_history(c, (int64_t)loss.size(), vp, lp) : kb_tpe_set_history(c, (int64_t)loss.size(), vp, lp);
+        if (rc) { s->uploaded.clear(); return fail(GRPC_INTERNAL, std::string(keep > 0 ? "kb_tpe_append_history: " : "kb_tpe_set_history: ") + kb_last_error(c)); }
+    }
     s->uploaded = ids;
     s->rows_uploaded += (long long)loss.size();
     s->history_dirty = false;
@@ -673,7 +699,17 @@ static Status SampleNext(kb_service *s, std::vector<KV> &assignments) {
     if (algo == "tpe" && n_observations(s) >= s->algo.n_startup) {
         Status st = PushHistory(s);
         if (st.code) return st;
-        if (kb_tpe_suggest(s->ctx, s->algo.n_ei, mix_seed((uint64_t)s->algo.seed, s->draw_counter++), v.data()))
+        const uint64_t seed = mix_seed((uint64_t)s->algo.seed, s->draw_counter++);
+        if (!s->peers.empty() && s->algo.n_ei >= KB_SERVICE_SHARD_MIN) {
+            // a large candidate set: every GPU draws and scores its index range of the one Philox stream, one NCCL
+            // collective merges the winners (kb_tpe_suggest with a communicator); all ranks return the same values
+            std::vector<std::vector<double>> vr(1 + s->peers.size(), std::vector<double>(D, 0.0));
+            kb_ctx *bad = nullptr;
+            const int64_t n_ei = s->algo.n_ei;
+            if (on_all_contexts(s, [&](int r, kb_ctx *c) { return kb_tpe_suggest(c, n_ei, seed, vr[(size_t)r].data()); }, &bad))
+                return fail(GRPC_INTERNAL, std::string("kb_tpe_suggest: ") + kb_last_error(bad));
+            v = vr[0];
+        } else if (kb_tpe_suggest(s->ctx, s->algo.n_ei, seed, v.data()))
             return engine_error(s, "kb_tpe_suggest");
     } else if (algo == "sobol") {
         std::vector<int> order(D);
@@ -729,13 +765,34 @@ static Status InitAtFirstRun(kb_service *s, const ExperimentMsg &e) {
     if (!ParseAlgorithm(e, a, err) || !ParseSearchSpace(e, sp, err)) return fail(GRPC_INTERNAL, kFailedStudy + err);
     if (sp.empty()) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + "empty search space");
     if (!s->ctx && kb_create(s->device, &s->ctx)) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(nullptr));
+    if (s->devices.size() > 1 && s->peers.empty()) {
+        // one context per further GPU, then one communicator over all of them (rank = position in the device list)
+        for (size_t r = 1; r < s->devices.size(); r++) {
+            kb_ctx *c = nullptr;
+            if (kb_create(s->devices[r], &c)) {
+                for (kb_ctx *p : s->peers) kb_destroy(p);
+                s->peers.clear();
+                return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(nullptr));
+            }
+            s->peers.push_back(c);
+        }
+        char uid[128];
+        if (kb_comm_unique_id(uid)) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(nullptr));
+        const int world = (int)s->devices.size();
+        kb_ctx *bad = nullptr;
+        if (on_all_contexts(s, [&](int r, kb_ctx *c) { return kb_comm_init(c, world, r, uid); }, &bad))
+            return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(bad));
+    }
     const size_t D = sp.size();
     std::vector<int32_t> kind(D), nch(D);
     std::vector<double> lo(D), hi(D), st(D);
     for (size_t i = 0; i < D; i++) { kind[i] = sp[i].kind; lo[i] = sp[i].low; hi[i] = sp[i].high; st[i] = sp[i].step; nch[i] = (int32_t)sp[i].choices.size(); }
-    if (kb_space_set(s->ctx, (int)D, kind.data(), lo.data(), hi.data(), st.data(), nch.data()))
-        return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(s->ctx));
-    kb_tpe_set_option(s->ctx, KB_OPT_MERGE_DUPLICATES, 1);  // same mixture, fewer terms (see katib_b200.h)
+    for (size_t r = 0; r <= s->peers.size(); r++) {
+        kb_ctx *c = r == 0 ? s->ctx : s->peers[r - 1];
+        if (kb_space_set(c, (int)D, kind.data(), lo.data(), hi.data(), st.data(), nch.data()))
+            return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(c));
+        kb_tpe_set_option(c, KB_OPT_MERGE_DUPLICATES, 1);  // same mixture, fewer terms (see katib_b200.h)
+    }
     s->algo = a; s->space = sp;
     s->maximize = e.objective_type != 1;  // toGoptunaDirection: MINIMIZE -> minimise, anything else -> maximise
     s->initialised = true;
@@ -773,9 +830,24 @@ extern "C" int kb_service_create(int device, kb_service **out) {
     *out = s;
     return KB_OK;
 }
+extern "C" int kb_service_create_multi(int n_devices, const int *devices, kb_service **out) {
+    if (!out) return KB_ERR_INVALID;
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > 64 || !devices) return kb_fail(nullptr, KB_ERR_INVALID, "kb_service_create_multi: n_devices outside [1, 64] or devices is NULL");
+    for (int i = 0; i < n_devices; i++)
+        for (int j = 0; j < i; j++)
+            if (devices[i] == devices[j]) return kb_fail(nullptr, KB_ERR_INVALID, "kb_service_create_multi: device %d listed twice", devices[i]);
+    kb_service *s = new kb_service();
+    s->device = devices[0];
+    s->devices.assign(devices, devices + n_devices);
+    *out = s;
+    return KB_OK;
+}
 extern "C" int kb_service_destroy(kb_service *s) {
     if (!s) return KB_OK;
-    if (s->ctx) kb_destroy(s->ctx);
+    // the communicator is torn down on all ranks together (ncclCommDestroy of one rank may wait for the others)
+    if (!s->peers.empty()) on_all_contexts(s, [](int, kb_ctx *c) { return kb_destroy(c); });
+    else if (s->ctx) kb_destroy(s->ctx);
     delete s;
     return KB_OK;
 }

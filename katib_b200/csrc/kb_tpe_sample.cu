@@ -110,8 +110,3 @@ extern "C" int kb_random_fill(kb_ctx *ctx, uint64_t seed, uint64_t first_index, 
     if (e != cudaSuccess) return kb_fail(ctx, KB_ERR_CUDA, "kb_random_fill: %s", cudaGetErrorString(e));
     return KB_OK;
 }
-
-// device-side draw used by kb_tpe_suggest (kb_tpe_score.cu): same stream, no host copy
-int kb_tpe_sample_into(kb_ctx *ctx, int64_t n, uint64_t seed, double *d_out, cudaStream_t s) {
-    return sample_launch(ctx, n, seed, d_out, s);
-}

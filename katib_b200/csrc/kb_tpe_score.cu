@@ -29,6 +29,22 @@
 #include "kb_tpe_sample.cuh"
 
 #define KB_EPS 1e-12
+// kb_tpe_suggest with a communicator: candidate counts from here on are sharded over the ranks (one collective); below
+// it every rank that calls works alone, so that a service may keep answering small requests on one GPU
+#define KB_SUGGEST_SHARD_MIN 65536
+
+// Where a kernel finds the f64 value of a candidate it has to remember (near ties): the caller's row-major matrix, or
+// -- when the candidates were drawn on the device straight into the staged columns and never stored -- the Philox
+// stream they came from (the draw is a pure function of seed, global index and parameter).
+struct KbRaw {
+    const double *cand;
+    unsigned long long seed;
+};
+__device__ __forceinline__ double kb_raw_value(const KbRaw &raw, const KbDim &dm, long long i_local, long long gidx, int D, int d) {
+    if (raw.cand) return raw.cand[(size_t)i_local * D + d];
+    const Philox ph(raw.seed);
+    return tpe_sample_one(dm, ph, (unsigned long long)gidx, d);
+}
 // Admission margin of the near-tie table, relative to max(1, |score|): several times the largest FP32
 // error measured against the FP64 oracle (continuous 7e-7, quantised 2e-6; tests/test_gpu_tpe.py prints them).
 #define KB_MARGIN_CONT 4e-6f
@@ -71,6 +87,31 @@ __device__ __forceinline__ void tma_bulk_g2s(void *dst_smem, const void *src_gme
 #define ST_DG 32
 #define ST_THREADS 256
 
+// one working-domain value -> what the scoring kernels read
+__device__ __forceinline__ float2 stage_value_cont(const KbDim &dm, double x) {
+    const double xn = (x - dm.lo) * (1.0 / (dm.hi - dm.lo));
+    const float xh = (float)xn;
+    return make_float2(xh, (float)(xn - (double)xh));
+}
+__device__ __forceinline__ float4 stage_value_quant(const KbDim &dm, double x) {
+    const double lo = dm.lo, hi = dm.hi, inv = 1.0 / (hi - lo), q = dm.q;
+    double ub = x + q / 2.0; ub = ub > hi ? hi : ub;
+    double lb = x - q / 2.0; lb = lb < lo ? lo : lb;
+    // bin midpoint (hi, lo) and half width, normalised; w = 1 when the bin is a full quantum
+    const double mn = (0.5 * (ub + lb) - lo) * inv, hn = 0.5 * (ub - lb) * inv;
+    const float mh = (float)mn, hwf = (float)hn;
+    float regular = fabs(hn - 0.5 * q * inv) <= 1e-9 * (q * inv) ? 1.f : 0.f;
+    // a full bin centred ON the quantisation grid: .w = grid index + 2 (look-up class of the score kernels)
+    const double gpos = (x - (lo + 0.5 * q)) / q, gidx = rint(gpos);
+    if (regular != 0.f && fabs(gpos - gidx) <= 1e-9 && gidx >= 0.0 && gidx < 16384.0) regular = (float)(gidx + 2.0);
+    return make_float4(mh, (float)(mn - (double)mh), hwf, regular);
+}
+// categorical selection key: (rank+1 : 13 bits) | (~call-local index : 32 bits) | (choice : 12 bits)
+__device__ __forceinline__ unsigned long long cat_key(const KbDim &dm, int c, long long local_index) {
+    return ((unsigned long long)(unsigned)(dm.cat_rank[c] + 1) << 44) | ((unsigned long long)(~(unsigned)local_index) << 12) |
+           (unsigned long long)c;
+}
+
 __global__ void __launch_bounds__(ST_THREADS)
 tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict__ cand, int n, long long chunk_cap,
                  float2 *__restrict__ stage_cont, float4 *__restrict__ stage_quant, const int *__restrict__ slot_of_dim,
@@ -94,10 +135,7 @@ tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict
                     int c = (int)tile[dd][r];
                     c = c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c);
                     if (scores_out) scores_out[(size_t)(row0 + r) * D + d] = dm.cat_score[c];
-                    // (rank+1 : 13 bits) | (~call-local index : 32 bits) | (choice : 12 bits)
-                    unsigned long long key = ((unsigned long long)(unsigned)(dm.cat_rank[c] + 1) << 44) |
-                                             ((unsigned long long)(~(unsigned)(local_base + row0 + r)) << 12) |
-                                             (unsigned long long)c;
+                    const unsigned long long key = cat_key(dm, c, local_base + row0 + r);
                     best = key > best ? key : best;
                 }
                 if (sel) {
@@ -108,30 +146,50 @@ tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict
                     if (lane == 0 && best) atomicMax(&sel[d].cat_best, best);
                 }
             } else {
-                const double lo = dm.lo, hi = dm.hi, inv = 1.0 / (hi - lo), q = dm.q;
+                const bool quant = dm.q > 0.0;
                 for (int r = lane; r < rows; r += 32) {
                     const double x = tile[dd][r];
-                    if (q > 0.0) {
-                        double ub = x + q / 2.0; ub = ub > hi ? hi : ub;
-                        double lb = x - q / 2.0; lb = lb < lo ? lo : lb;
-                        // bin midpoint (hi, lo) and half width, normalised; w = 1 when the bin is a full quantum
-                        double mn = (0.5 * (ub + lb) - lo) * inv, hn = 0.5 * (ub - lb) * inv;
-                        float mh = (float)mn, hwf = (float)hn;
-                        float regular = fabs(hn - 0.5 * q * inv) <= 1e-9 * (q * inv) ? 1.f : 0.f;
-                        // a full bin centred ON the quantisation grid: .w = grid index + 2 (look-up class of the score kernel)
-                        const double gpos = (x - (lo + 0.5 * q)) / q, gidx = rint(gpos);
-                        if (regular != 0.f && fabs(gpos - gidx) <= 1e-9 && gidx >= 0.0 && gidx < 16384.0) regular = (float)(gidx + 2.0);
-                        stage_quant[(size_t)slot * chunk_cap + row0 + r] = make_float4(mh, (float)(mn - (double)mh), hwf, regular);
-                    } else {
-                        double xn = (x - lo) * inv;
-                        float xh = (float)xn;
-                        stage_cont[(size_t)slot * chunk_cap + row0 + r] = make_float2(xh, (float)(xn - (double)xh));
-                    }
+                    if (quant) stage_quant[(size_t)slot * chunk_cap + row0 + r] = stage_value_quant(dm, x);
+                    else stage_cont[(size_t)slot * chunk_cap + row0 + r] = stage_value_cont(dm, x);
                 }
             }
         }
         __syncthreads();
     }
+}
+
+// The same staging for candidates that do not exist yet: kb_tpe_suggest draws candidate (first + i) of parameter d from
+// the Philox stream (tpe_sample_one, the values kb_tpe_sample_candidates would return for the same seed) and writes it
+// straight into the staged column -- the n x D f64 candidate matrix is never materialised.  One CTA = 256 consecutive
+// candidates of ONE parameter (blockIdx.y), so the kind branch is uniform and the column stores coalesce.
+#define SS_THREADS 256
+__global__ void __launch_bounds__(SS_THREADS)
+tpe_sample_stage_kernel(const KbDim *__restrict__ dims, int n, long long chunk_cap, unsigned long long seed, long long first,
+                        float2 *__restrict__ stage_cont, float4 *__restrict__ stage_quant, const int *__restrict__ slot_of_dim,
+                        KbSelect *sel, long long local_base) {
+    const int d = blockIdx.y;
+    const KbDim &dm = dims[d];
+    const int slot = slot_of_dim[d];
+    const int i = blockIdx.x * SS_THREADS + threadIdx.x;
+    const Philox ph(seed);
+    if (dm.kind == KB_CATEGORICAL) {
+        unsigned long long best = 0ull;
+        if (i < n) {
+            int c = (int)tpe_sample_one(dm, ph, (unsigned long long)(first + i), d);
+            c = c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c);
+            best = cat_key(dm, c, local_base + i);
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other > best ? other : best;
+        }
+        if ((threadIdx.x & 31) == 0 && best) atomicMax(&sel[d].cat_best, best);
+        return;
+    }
+    if (i >= n) return;
+    const double x = tpe_sample_one(dm, ph, (unsigned long long)(first + i), d);
+    if (dm.q > 0.0) stage_quant[(size_t)slot * chunk_cap + i] = stage_value_quant(dm, x);
+    else stage_cont[(size_t)slot * chunk_cap + i] = stage_value_cont(dm, x);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -156,8 +214,9 @@ __device__ __forceinline__ void tie_insert(KbTie *tab, float *tab_score, unsigne
 // block-wide: publish the block maximum, derive the admission threshold, insert the near ties
 template <int R, int THREADS>
 __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_base, int n, long long idx_base, int d,
-                                               int D, int numeric_slot, KbSelect *sel, KbTie *tie, float *tie_score,
-                                               unsigned int slots, float margin, const double *__restrict__ cand_raw) {
+                                               int D, const KbDim &dm, KbSelect *sel, KbTie *tie, float *tie_score,
+                                               unsigned int slots, float margin, KbRaw cand_raw) {
+    const int numeric_slot = dm.numeric_slot;
     __shared__ float s_wmax[THREADS / 32];
     __shared__ float s_thr;
     float best = -INFINITY;
@@ -187,7 +246,7 @@ __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_ba
     for (int r = 0; r < R; r++) {
         int i = tile_base + r * THREADS + threadIdx.x;
         if (i < n && sc[r] >= thr) {
-            unsigned long long key = (unsigned long long)__double_as_longlong(cand_raw[(size_t)i * D + d]);
+            unsigned long long key = (unsigned long long)__double_as_longlong(kb_raw_value(cand_raw, dm, i, idx_base + i, D, d));
             tie_insert(tab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + i), sc[r]);
         }
     }
@@ -322,7 +381,7 @@ __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                       const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                       KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
-                      const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
+                      KbRaw cand_raw, double *__restrict__ scores_out) {
     __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     const int slot = blockIdx.y;
@@ -389,7 +448,7 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
         int i = tile_base + r * SC_THREADS + threadIdx.x;
         if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
     }
-    if (sel) select_publish<SC_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
+    if (sel) select_publish<SC_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm, sel, tie, tie_score, slots,
                                                   KB_MARGIN_CONT, cand_raw);
 }
 
@@ -477,7 +536,7 @@ __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                              const float2 *__restrict__ sorted, const int32_t *__restrict__ perm, long long chunk_cap, int n,
                              long long idx_base, int D, KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
-                             const double *__restrict__ cand_raw, double *__restrict__ scores_out) {
+                             KbRaw cand_raw, double *__restrict__ scores_out) {
     __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     __shared__ PruneSeg s_seg[4];
@@ -617,7 +676,7 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
 #pragma unroll
     for (int r = 0; r < SC_R; r++) {
         if (orig[r] >= 0 && sc[r] >= thr) {
-            const unsigned long long key = (unsigned long long)__double_as_longlong(cand_raw[(size_t)orig[r] * D + d]);
+            const unsigned long long key = (unsigned long long)__double_as_longlong(kb_raw_value(cand_raw, dm, orig[r], idx_base + orig[r], D, d));
             tie_insert(ttab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + orig[r]), sc[r]);
         }
     }
@@ -667,7 +726,7 @@ __global__ void __launch_bounds__(SC_THREADS, SQ_MINB)
 tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
                        const float4 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                        KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
-                       const double *__restrict__ cand_raw, double *__restrict__ scores_out,
+                       KbRaw cand_raw, double *__restrict__ scores_out,
                        const int *__restrict__ tile_flags, int tiles_stride) {
     __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
@@ -878,7 +937,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
         int i = tile_base + r * SC_THREADS + threadIdx.x;
         if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
     }
-    if (sel) select_publish<SQ_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
+    if (sel) select_publish<SQ_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm, sel, tie, tie_score, slots,
                                                   KB_MARGIN_QUANT, cand_raw);
 }
 
@@ -906,7 +965,7 @@ __global__ void __launch_bounds__(SC_THREADS, 3)
 tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restrict__ quant_dims,
                             const float4 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                             KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
-                            const double *__restrict__ cand_raw, double *__restrict__ scores_out, int *tile_flags,
+                            KbRaw cand_raw, double *__restrict__ scores_out, int *tile_flags,
                             int tiles_stride) {
     __shared__ __align__(128) float s_w[2][SQG_WCHUNK];
     __shared__ __align__(16) float4 s_other[SQG_OTHER * 2];
@@ -1091,7 +1150,7 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
         const int i = tile_base + r * SC_THREADS + threadIdx.x;
         if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
     }
-    if (sel) select_publish<SQG_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm.numeric_slot, sel, tie, tie_score, slots,
+    if (sel) select_publish<SQG_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm, sel, tie, tie_score, slots,
                                                    KB_MARGIN_QUANT, cand_raw);
 }
 
@@ -1341,7 +1400,6 @@ int kb_tpe_free(kb_ctx *ctx) {
     cudaFree(ctx->d_stage_sorted); cudaFree(ctx->d_perm); cudaFree(ctx->d_bucket);
     ctx->d_stage_sorted = nullptr; ctx->d_perm = nullptr; ctx->d_bucket = nullptr;
     cudaFree(ctx->d_qflags); ctx->d_qflags = nullptr;
-    cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
     cudaFree(ctx->d_tie_score); cudaFree(ctx->d_tie_list); cudaFree(ctx->d_tie_count); cudaFree(ctx->d_slot_of_dim); cudaFree(ctx->d_numeric_dims);
     if (ctx->h_win) cudaFreeHost(ctx->h_win);
     ctx->d_tie_score = nullptr; ctx->d_tie_list = nullptr; ctx->d_tie_count = nullptr; ctx->tie_slots = 0; ctx->d_slot_of_dim = nullptr; ctx->d_numeric_dims = nullptr;
@@ -1414,15 +1472,23 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
 }
 
 // launch stage + scoring kernels for one resident chunk
-static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand, int n, long long idx_base, long long local_base, bool select,
-                            double *d_scores, cudaStream_t s) {
+// d_cand_in == nullptr: the chunk's candidates are global indices [idx_base, idx_base + n) of the Philox stream `seed`,
+// drawn straight into the staged columns (kb_tpe_suggest)
+static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long long idx_base, long long local_base, bool select,
+                            double *d_scores, cudaStream_t s, unsigned long long seed = 0) {
     kb_ctx *sc = ctx;
     const int D = ctx->D;
     KbSelect *sel = select ? ctx->d_sel : nullptr;
-    { KbProf pf(ctx, 0, s);
-    tpe_stage_kernel<<<(n + ST_ROWS - 1) / ST_ROWS, ST_THREADS, 0, s>>>(ctx->d_dims, D, d_cand, n, ctx->chunk_cap,
-                                                                        ctx->d_stage_cont, ctx->d_stage_quant,
-                                                                        sc->d_slot_of_dim, sel, local_base, d_scores);
+    const KbRaw d_cand = {d_cand_in, seed};
+    if (d_cand_in) {
+        KbProf pf(ctx, 0, s);
+        tpe_stage_kernel<<<(n + ST_ROWS - 1) / ST_ROWS, ST_THREADS, 0, s>>>(ctx->d_dims, D, d_cand_in, n, ctx->chunk_cap,
+                                                                            ctx->d_stage_cont, ctx->d_stage_quant,
+                                                                            sc->d_slot_of_dim, sel, local_base, d_scores);
+    } else {
+        KbProf pf(ctx, 6, s);
+        tpe_sample_stage_kernel<<<dim3((unsigned)((n + SS_THREADS - 1) / SS_THREADS), (unsigned)D), SS_THREADS, 0, s>>>(
+            ctx->d_dims, n, ctx->chunk_cap, seed, idx_base, ctx->d_stage_cont, ctx->d_stage_quant, sc->d_slot_of_dim, sel, local_base);
     }
     KB_LAUNCH_CHECK(ctx);
     if (ctx->n_cont > 0 && ctx->tpe_prune) {
@@ -1499,7 +1565,7 @@ static int tpe_reset_selection(kb_ctx *ctx, cudaStream_t s) {
 }
 
 static int tpe_finish_selection(kb_ctx *ctx, long long idx_base, int64_t *out_index, double *out_value, double *out_score,
-                                cudaStream_t s) {
+                                cudaStream_t s, bool collective = true) {
     kb_ctx *sc = ctx;
     const int D = ctx->D;
     {
@@ -1520,6 +1586,7 @@ static int tpe_finish_selection(kb_ctx *ctx, long long idx_base, int64_t *out_in
     }
     int world = 1, rank = 0;
     kb_comm_world(ctx, &world, &rank);
+    if (!collective) world = 1;
     if (world > 1) {
         // winners and the status row go through ONE collective: a rank whose near-tie table overflowed is seen by all
         // ranks before any of them trusts the merged winners, and all of them repeat the pass (or fail) together
@@ -1648,7 +1715,6 @@ extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const dou
 }
 
 // Full tpe.Sampler.Sample for every parameter: draw on the device (kb_tpe_sample.cu), score, select.
-int kb_tpe_sample_into(kb_ctx *ctx, int64_t n, uint64_t seed, double *d_out, cudaStream_t s);
 
 extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t seed, double *out_value) {
     if (!ctx) return KB_ERR_INVALID;
@@ -1660,16 +1726,17 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
     if (!out_value) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest: out_value is NULL");
     cudaStream_t s = ctx->stream;
     const int64_t n = n_ei_candidates;
+    int world = 1, rank = 0;
+    kb_comm_world(ctx, &world, &rank);
+    const bool sharded = world > 1 && n >= KB_SUGGEST_SHARD_MIN;
     {   // small problems (Katib's own: 24 candidates): the fused single-kernel path
-        int world = 1, rank = 0;
-        kb_comm_world(ctx, &world, &rank);
         int64_t kmax = 1;
         for (int d = 0; d < ctx->D; d++) {
             const KbDim &k = ctx->h_dims[(size_t)d];
             if (k.kind != KB_CATEGORICAL) kmax = std::max<int64_t>(kmax, (int64_t)k.K[0] + k.K[1]);
         }
         const char *off = getenv("KB_SUGGEST_SMALL");
-        if (world == 1 && n <= SM_MAX_CAND && n * kmax <= (1 << 18) && !(off && off[0] == '0')) {
+        if (n <= SM_MAX_CAND && n * kmax <= (1 << 18) && !(off && off[0] == '0')) {
             if (!ctx->d_win) KB_CUDA(ctx, cudaMalloc(&ctx->d_win, sizeof(KbWinner) * (size_t)(ctx->D + 1)));
             if (!ctx->h_win) KB_CUDA(ctx, cudaMallocHost(&ctx->h_win, sizeof(KbWinner) * (size_t)(ctx->D + 1)));
             {
@@ -1683,23 +1750,28 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
             return KB_OK;
         }
     }
-    if (n * ctx->D > ctx->suggest_cap) {
-        cudaFree(ctx->d_suggest); ctx->d_suggest = nullptr; ctx->suggest_cap = 0;
-        KB_CUDA(ctx, cudaMalloc(&ctx->d_suggest, sizeof(double) * (size_t)n * ctx->D));
-        ctx->suggest_cap = n * ctx->D;
+    // The staged pipeline, candidates drawn chunk by chunk straight into the staged columns (tpe_sample_stage_kernel): no
+    // n x D candidate matrix exists, the scratch is the staging of one chunk whatever n is.  With a communicator and
+    // n >= KB_SUGGEST_SHARD_MIN this rank draws and scores only its index range of the one global Philox stream; the
+    // winners are merged by the collective in tpe_finish_selection, so every rank returns the same values -- those of
+    // the unsharded call.
+    int64_t first = 0, count = n;
+    if (sharded) {
+        const int64_t base = n / world, extra = n % world;  // katib_b200/sharding.py: shard_range
+        first = rank * base + std::min<int64_t>(rank, extra);
+        count = base + (rank < extra ? 1 : 0);
     }
-    double *d_cand = ctx->d_suggest;
-    int rc = kb_tpe_sample_into(ctx, n, seed, d_cand, s);
-    const int64_t rows = n < KB_CHUNK_ROWS ? n : KB_CHUNK_ROWS;
+    const int64_t rows = std::max<int64_t>(1, std::min<int64_t>(count, KB_CHUNK_ROWS));
+    int rc = KB_OK;
     for (int attempt = 0; !rc; attempt++) {
-        rc = tpe_ensure_scratch(ctx, rows, n, false, false);
+        rc = tpe_ensure_scratch(ctx, rows, count, false, false);
         if (!rc) rc = tpe_reset_selection(ctx, s);
         const int64_t cap = ctx->chunk_cap;
-        for (int64_t off = 0; !rc && off < n; off += cap) {
-            const int m = (int)(n - off < cap ? n - off : cap);
-            rc = tpe_launch_chunk(ctx, d_cand + (size_t)off * ctx->D, m, off, off, true, nullptr, s);
+        for (int64_t off = 0; !rc && off < count; off += cap) {
+            const int m = (int)(count - off < cap ? count - off : cap);
+            rc = tpe_launch_chunk(ctx, nullptr, m, first + off, off, true, nullptr, s, seed);
         }
-        if (!rc) rc = tpe_finish_selection(ctx, 0, nullptr, out_value, nullptr, s);
+        if (!rc) rc = tpe_finish_selection(ctx, first, nullptr, out_value, nullptr, s, sharded);
         if (!tpe_retry_overflow(ctx, rc, attempt)) break;
         rc = KB_OK;
     }
