@@ -9,7 +9,7 @@ communicator set, and scores everything again on a second, communicator-less con
 
 Cases: (1) mixed space, the best candidate of every parameter copied to a higher index inside the other shards and one
 row duplicated across each shard boundary (the lower global index must win on every rank), host-buffer and
-device-pointer entry points, merged + pruned options; (2) empty history = every score equal: all ranks overflow their
+device-pointer entry points, merged + pruned options, kb_tpe_suggest sharded against unsharded; (2) empty history = every score equal: all ranks overflow their
 near-tie tables, repeat the pass together, index 0 wins; (3) a flat landscape where only the LAST rank's slice has
 many distinct values: that rank alone overflows, and every rank must still repeat the pass (the status row travels
 with the winners) and agree."""
@@ -90,6 +90,13 @@ def main():
     check("case1 merged+pruned: sharded == oracle", list(idx_m) == best, f"{list(idx_m)} vs {best}")
     for opt in ((1, 0), (2, 0)):
         sharded.tpe_set_option(*opt)
+    # kb_tpe_suggest with a communicator: every rank draws and scores its index range of ONE Philox stream and all of
+    # them return what the single-GPU call returns (200 000 candidates: above the sharding threshold)
+    v_full = full.tpe_suggest(200_000, seed=77)
+    v_sh = sharded.tpe_suggest(200_000, seed=77)
+    check("case1 suggest: sharded == single", np.array_equal(v_sh, v_full), f"{v_sh} vs {v_full}")
+    if rank == 0:  # below the threshold there is no collective: one rank may call alone
+        check("case1 suggest small: lone rank", np.array_equal(sharded.tpe_suggest(24, seed=5), full.tpe_suggest(24, seed=5)))
 
     # ---- case 2: empty history, every score is exactly 0: all ranks overflow, repeat together, index 0 wins
     kinds2, lows2, highs2 = [kb.KB_UNIFORM, kb.KB_INT], [0.0, 0], [1.0, 9]

@@ -139,3 +139,21 @@ def test_step_int_suggestions_stay_on_the_declared_grid():
     r = ctx.random_fill(seed=3, first=0, n=500)
     assert set(np.unique(r[:, 0])) <= {1, 3, 5, 7, 9} and set(np.unique(r[:, 1])) <= {-7, -4, -1, 2, 5, 8}
     ctx.close()
+
+
+def test_suggest_streams_its_candidates_chunk_by_chunk(monkeypatch):
+    """kb_tpe_suggest never stores its candidates: each chunk is drawn straight into the staging columns.  With the
+    chunk forced down to 2^16 rows a 200 000-candidate call crosses three chunk boundaries and must still return the
+    winners of kb_tpe_score_select over the stored candidates of the same seed (near ties regenerate their value from
+    the stream)."""
+    monkeypatch.setenv("KB_CHUNK_LOG2", "16")
+    ctx = kb.Context(0)  # a fresh context: its staging is sized by the first call, i.e. to 2^16 rows
+    sp, vals, loss = _setup(ctx, 500, 29)
+    n_ei = 200_000
+    out = ctx.tpe_suggest(n_ei, seed=4242)
+    cand = ctx.tpe_sample_candidates(n_ei, seed=4242)
+    idx, val, sc = ctx.tpe_score_select(cand)
+    assert np.array_equal(out, val), (out, val)
+    ctx.tpe_set_option(2, 1)  # the pruned continuous kernel regenerates through its permutation
+    assert np.array_equal(ctx.tpe_suggest(n_ei, seed=4242), val)
+    ctx.close()

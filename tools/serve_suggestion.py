@@ -5,7 +5,7 @@ grpc.health.v1.Health/Check -> SERVING (main.go:37-41), and forwards the request
 Nothing is parsed or computed here: the protobuf handling and all arithmetic live in libkatib_b200.so.
 The production front end is the Go shim of INTEGRATION.md; this file exists for wire-level tests and demos.
 
-    python tools/serve_suggestion.py [--port 6789] [--device 0]
+    python tools/serve_suggestion.py [--port 6789] [--device 0 | --devices 0,1,2,3]
 """
 import argparse
 import os
@@ -22,8 +22,8 @@ SERVING = b"\x08\x01"  # HealthCheckResponse{status: SERVING}
 MAX_MSG = 256 << 20    # the reference runs with grpc-go's 4 MiB default; a 10k-trial request needs more
 
 
-def make_server(port, device=0, host="0.0.0.0"):
-    svc = kb.Service(device)
+def make_server(port, device=0, host="0.0.0.0", devices=None):
+    svc = kb.Service(device, devices=devices)  # several devices: kb_service_create_multi (one service, sharded TPE)
 
     def get_suggestions(request, context):
         code, reply, msg = svc.get_suggestions(request)
@@ -55,8 +55,10 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--port", type=int, default=6789)
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--devices", default="", help="comma-separated device list, e.g. 0,1 (overrides --device)")
     a = ap.parse_args()
-    server, port, _ = make_server(a.port, a.device)
+    devs = [int(x) for x in a.devices.split(",") if x.strip()] or None
+    server, port, _ = make_server(a.port, a.device, devices=devs)
     server.start()
     print(f"katib-b200 suggestion service listening on :{port}", flush=True)
     server.wait_for_termination()
