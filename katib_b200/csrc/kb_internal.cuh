@@ -55,9 +55,14 @@ struct KbDim {
     // point, qruns[side][n_runs] = {grid code, first index into qw, length, 0} -- a run's table value is fetched once
     // per candidate and every component of it costs half a packed FFMA.  All other components (the prior, wide sigmas,
     // anything off the grid) sit in tabw[side][Kw] in the usual two-float4 form.  Kn / Kw hold the two counts.
+    // Runs are padded with zero weights to multiples of four entries (Kn counts the padded array); a run entry is
+    // {grid code, first index, padded length, real length}.  Other components whose mu is on the grid as well carry
+    // 0x40000000 | row << 16 | grid index in their .w and own row `row` of lut2[side] (2G - 1 floats per row): their
+    // bin integral at every integer grid offset, with their own sigma.
     float *qw[2];
     int4 *qruns[2];
     int32_t n_runs[2];
+    float *lut2[2];
     // continuous parameters, KB_OPT_PRUNE_FAR: the same table split into the components whose sigma sits on the
     // magic-clip floor ("narrow", still sorted by mu, Kn entries padded to KB_TABLE_PAD) and the rest ("wide", Kw
     // entries, padded).  A narrow component further than prune_w (normalised) from a candidate contributes less than
@@ -67,6 +72,7 @@ struct KbDim {
     float prune_w[2];         // 7.75 sigma_floor of the side, normalised
 };
 #define KB_LUT_MAX 256        // floats per (parameter, side): grids of up to 128 points
+#define KB_LUT2_FLOATS 8192   // floats per (quantised parameter, side) for the per-component rows (32 rows of a 128-point grid)
 #ifndef KB_QF_DEG
 #define KB_QF_DEG 11
 #endif

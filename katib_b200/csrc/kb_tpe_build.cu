@@ -372,7 +372,9 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     }
     // Quantised parameters: split the entries, in order, into the look-up class (grid code != 0: dense weights + run
     // table, see KbDim::qw) and the rest (tabw).  A stable partition by a block scan over per-thread segments, then a
-    // second scan over the look-up-class entries that numbers the runs of equal grid code.
+    // second scan over the look-up-class entries that numbers the runs of equal grid code.  Every run is padded with
+    // zero weights to a multiple of four entries and starts on a multiple of four, so that the grid kernel reads it
+    // as whole LDS.128s.
     if (quant) {
         __syncthreads();
         float *qw = dm.qw[side];
@@ -392,16 +394,41 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
         const int Kg = s_int[nt - 1], Ko = K - Kg;
         int bg = s_int[tid] - c, bo = b0 - bg;
         __syncthreads();
+        // The other components that sit ON the grid too (wider sigma: the whole below side of a dense history) get a
+        // table row of their own: for an on-grid candidate their bin integral depends only on the integer offset as
+        // well, with the component's own sigma.  Rows are handed out in table order while the budget lasts
+        // (KB_LUT2_FLOATS); the entry's .w then carries 0x40000000 | row << 16 | grid index of mu.
+        const int rowlen = 2 * G - 1;
+        const int max_rows = G > 0 ? min(KB_LUT2_FLOATS / rowlen, 255) : 0;
         for (int j = b0; j < b1; j++) {
             const float4 Bj = tab[2 * j + 1];
             const int code = __float_as_int(Bj.w);
-            if (code != 0) { qw[bg] = fabsf(Bj.z); idx[bg] = (uint32_t)code; bg++; }
-            else { to[2 * bo] = tab[2 * j]; to[2 * bo + 1] = Bj; bo++; }
+            if (code != 0) { keys[bg] = (double)fabsf(Bj.z); idx[bg] = (uint32_t)code; bg++; }
+            else {
+                float4 Bo = Bj;
+                if (bo < max_rows) {
+                    const double gi = (mu[j] - (low + 0.5 * dm.q)) / dm.q, gr = rint(gi);
+                    if (fabs(gi - gr) <= 1e-9 && gr >= 0.0 && gr < (double)G) Bo.w = __int_as_float(0x40000000 | (bo << 16) | (int)gr);
+                }
+                keys[Kg + bo] = sg[j];  // for the row below (keys[] holds K <= npad entries)
+                to[2 * bo] = tab[2 * j]; to[2 * bo + 1] = Bo; bo++;
+            }
         }
         const float4 Z = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int j = Kg + tid; j < (Kg + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) qw[j] = 0.f;
         for (int j = Ko + tid; j < (Ko + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { to[2 * j] = Z; to[2 * j + 1] = Z; }
         __syncthreads();
+        {   // rows of the second table: row o belongs to other-entry o (only entries with the 0x40000000 mark are read)
+            const int nrow = min(Ko, max_rows);
+            float *lut2 = dm.lut2[side];
+            for (int e = tid; e < nrow * rowlen; e += nt) {
+                const int o = e / rowlen, k = e - o * rowlen;
+                double den = sqrt(2.0) * keys[Kg + o];
+                if (den < KB_EPS) den = KB_EPS;
+                const double rr = 1.0 / den, h = 0.5 * dm.q * rr;
+                const double y = fabs((double)(k - (G - 1))) * dm.q * rr;
+                lut2[e] = (float)(erfc(y - h) - erfc(y + h));
+            }
+        }
         const int seg2 = (Kg + nt - 1) / nt, g0 = min(Kg, tid * seg2), g1 = min(Kg, g0 + seg2);
         int h = 0;
         for (int p = g0; p < g1; p++) h += (p == 0 || idx[p] != idx[p - 1]) ? 1 : 0;
@@ -414,12 +441,35 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
             __syncthreads();
         }
         const int n_runs = s_int[nt - 1];  // <= grid points <= KB_LUT_MAX / 2 (codes are non-decreasing in table order)
-        int r = s_int[tid] - h;
-        for (int p = g0; p < g1; p++)
-            if (p == 0 || idx[p] != idx[p - 1]) { runs[r] = make_int4((int)idx[p], p, 0, 0); r++; }
+        const int r0 = s_int[tid] - h;     // runs that begin before this thread's segment
+        {
+            int r = r0;
+            for (int p = g0; p < g1; p++)
+                if (p == 0 || idx[p] != idx[p - 1]) { runs[r] = make_int4((int)idx[p], p, 0, 0); r++; }
+        }
         __syncthreads();
         for (int q = tid; q < n_runs; q += nt) runs[q].z = (q + 1 < n_runs ? runs[q + 1].y : Kg) - runs[q].y;
-        if (tid == 0) { dm.Kn[side] = Kg; dm.Kw[side] = Ko; dm.n_runs[side] = n_runs; }
+        __syncthreads();
+        if (tid == 0) {  // padded starts (at most 128 runs)
+            int ps = 0;
+            for (int q = 0; q < n_runs; q++) { runs[q].w = ps; ps += (runs[q].z + 3) & ~3; }
+            s_int[0] = ps;
+        }
+        __syncthreads();
+        const int Kgp = s_int[0];
+        {   // scatter the weights to their padded places; the run of position p is r0 - 1 + (heads met so far)
+            int r = r0 - 1;
+            for (int p = g0; p < g1; p++) {
+                if (p == 0 || idx[p] != idx[p - 1]) r++;
+                qw[runs[r].w + (p - runs[r].y)] = (float)keys[p];
+            }
+        }
+        for (int q = tid; q < n_runs; q += nt)
+            for (int e = runs[q].w + runs[q].z; e < runs[q].w + ((runs[q].z + 3) & ~3); e++) qw[e] = 0.f;
+        for (int e = Kgp + tid; e < (Kgp + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; e += nt) qw[e] = 0.f;
+        __syncthreads();
+        for (int q = tid; q < n_runs; q += nt) { const int4 rq = runs[q]; runs[q] = make_int4(rq.x, rq.w, (rq.z + 3) & ~3, rq.z); }
+        if (tid == 0) { dm.Kn[side] = Kgp; dm.Kw[side] = Ko; dm.n_runs[side] = n_runs; }
     }
     // KB_OPT_PRUNE_FAR (continuous parameters): the same entries split, in order, into floor-sigma ("narrow") and
     // other ("wide") components -- see KbDim::tabn.  A stable partition by a block scan over per-thread segments.
@@ -562,7 +612,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
         else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 6 * sizeof(float4)) + KB_LUT_MAX * sizeof(float) +
-                           (KB_LUT_MAX / 2) * sizeof(int4));
+                           (KB_LUT_MAX / 2) * sizeof(int4) + (k.q > 0 ? KB_LUT2_FLOATS * sizeof(float) : 0));
     }
     if (bytes > ctx->tabmem_bytes) {
         cudaFree(ctx->d_tabmem); ctx->d_tabmem = nullptr;
@@ -590,6 +640,8 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
                 k.lut[side] = (float *)p; p += KB_LUT_MAX * sizeof(float);
                 k.qruns[side] = (int4 *)p; p += (KB_LUT_MAX / 2) * sizeof(int4);
                 k.qw[side] = (float *)k.tabn[side];  // quantised parameters have no "narrow" table: the area holds qw
+                k.lut2[side] = nullptr;
+                if (k.q > 0) { k.lut2[side] = (float *)p; p += KB_LUT2_FLOATS * sizeof(float); }
             }
         }
     }

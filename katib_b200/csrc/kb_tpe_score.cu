@@ -956,7 +956,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
 #define SQG_R 8
 #define SQG_WCHUNK 4096     // weights per shared-memory stage (16 KB), two stages
 #ifndef SQG_FLUSH
-#define SQG_FLUSH 128       // components per FP32 partial sum before it is folded into the (hi, lo) pair
+#define SQG_FLUSH 128       // components per FP32 partial sum before it is folded into the (hi, lo) pair (multiple of 4)
 #endif
 #define SQG_OTHER 64        // other-class entries per shared-memory pass
 static_assert(SQG_R == SQ_R, "the grid kernel and tpe_score_quant_kernel must agree on the tile size");
@@ -1031,11 +1031,13 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
         // ---- the other components (arithmetic classes), while the first weight stages are in flight
         {
             float xm[SQG_R], xl[SQG_R], hw[SQG_R];
+            int gi[SQG_R];  // grid index of the candidate
 #pragma unroll
             for (int r = 0; r < SQG_R; r++) {
                 const int i = tile_base + r * SC_THREADS + threadIdx.x;
                 const float4 v = i < n ? my_stage[i] : make_float4(0.5f, 0.f, dm.qf_hw[0], 2.f);
                 xm[r] = v.x; xl[r] = v.y; hw[r] = v.z;
+                gi[r] = (int)v.w - 2;
             }
             const float qn = (float)(dm.q / (dm.hi - dm.lo));
             const int Kop = (Ko + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
@@ -1048,6 +1050,16 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
                     const float4 A = s_other[2 * j], B = s_other[2 * j + 1];
                     const float wj = fabsf(B.z);
                     if (wj == 0.f) continue;  // padding
+                    const int code2 = __float_as_int(B.w);
+                    if (code2 & 0x40000000) {  // mu on the grid: the component's own table row (KbDim::lut2), one load each
+                        const float *row = dm.lut2[side] + ((code2 >> 16) & 0xFF) * (2 * G - 1) + (G - 1) - (code2 & 0xFFFF);
+#pragma unroll
+                        for (int r = 0; r < SQG_R; r++) {
+                            const float tv = __ldg(row + gi[r]);
+                            if (r & 1) a32[r / 2].y = fmaf(wj, tv, a32[r / 2].y); else a32[r / 2].x = fmaf(wj, tv, a32[r / 2].x);
+                        }
+                        continue;
+                    }
                     if (A.z * qn < QUANT_WIDE_THR) {  // narrow bin: series about the midpoint
 #pragma unroll
                         for (int r = 0; r < SQG_R; r++) {
@@ -1092,20 +1104,14 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
                     const float tv = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(s_lut) + (xo[r] - (uint32_t)run.x));
                     if (r & 1) tvp[r / 2].y = tv; else tvp[r / 2].x = tv;
                 }
+                // runs start on multiples of four and are zero-padded to multiples of four: whole LDS.128s only
                 int j = a;
                 while (j < b) {
                     const int m = min(b - j, SQG_FLUSH - since);
-                    const float *wp = w + j;
-                    int k = 0;
-                    const int head = min(m, (4 - (j & 3)) & 3);
-                    for (; k < head; k++) {
-                        const float2 w2 = make_float2(wp[k], wp[k]);
-#pragma unroll
-                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(w2, tvp[p], a32[p]);
-                    }
+                    const float4 *wp = reinterpret_cast<const float4 *>(w + j);
 #pragma unroll 2
-                    for (; k + 4 <= m; k += 4) {
-                        const float4 w4 = *reinterpret_cast<const float4 *>(wp + k);  // one broadcast LDS.128: four weights
+                    for (int k = 0; k < m / 4; k++) {
+                        const float4 w4 = wp[k];  // one broadcast LDS.128: four weights
                         const float2 wa = make_float2(w4.x, w4.x), wb = make_float2(w4.y, w4.y);
                         const float2 wc = make_float2(w4.z, w4.z), wd = make_float2(w4.w, w4.w);
 #pragma unroll
@@ -1116,11 +1122,6 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
                         for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(wc, tvp[p], a32[p]);
 #pragma unroll
                         for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(wd, tvp[p], a32[p]);
-                    }
-                    for (; k < m; k++) {
-                        const float2 w2 = make_float2(wp[k], wp[k]);
-#pragma unroll
-                        for (int p = 0; p < SQG_R / 2; p++) a32[p] = __ffma2_rn(w2, tvp[p], a32[p]);
                     }
                     j += m; since += m;
                     if (since >= SQG_FLUSH) { flush(); since = 0; }
