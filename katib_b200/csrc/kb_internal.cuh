@@ -168,6 +168,9 @@ struct kb_ctx {
     cudaEvent_t ev_build = nullptr;  // recorded on `stream` after every history build; caller streams wait on it
 
     uint32_t *d_sobol_v = nullptr;   // [32][KB_SOBOL_MAX_DIM] direction numbers, bit-major
+    double *d_sobol_buf[2] = {nullptr, nullptr};   // kb_sobol_fill: alternating chunk buffers (grow-only)
+    double *h_sobol_pin[2] = {nullptr, nullptr};   // ... and pinned staging for pageable destinations
+    size_t sobol_buf_bytes = 0, sobol_pin_bytes = 0;
 
     KbComm *comm = nullptr;
     KbCma *cma = nullptr;

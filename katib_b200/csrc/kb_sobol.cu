@@ -6,6 +6,9 @@
 // lanes run along the dimension so that every store instruction writes 256 contiguous bytes.  The
 // state at a group's first index comes from the closed form x_i = XOR_{b in gray(i)} v[b]; the next
 // SOBOL_P-1 points flip one direction number each (v[ctz(~i)]), the low four of which sit in registers.
+#include <algorithm>
+#include <thread>
+
 #include "kb_internal.cuh"
 #include "sobol_joe_kuo.inc"
 
@@ -87,6 +90,12 @@ static int sobol_tables(kb_ctx *ctx) {
 int kb_sobol_free(kb_ctx *ctx) {
     cudaFree(ctx->d_sobol_v);
     ctx->d_sobol_v = nullptr;
+    for (int i = 0; i < 2; i++) {
+        cudaFree(ctx->d_sobol_buf[i]); ctx->d_sobol_buf[i] = nullptr;
+        if (ctx->h_sobol_pin[i]) cudaFreeHost(ctx->h_sobol_pin[i]);
+        ctx->h_sobol_pin[i] = nullptr;
+    }
+    ctx->sobol_buf_bytes = ctx->sobol_pin_bytes = 0;
     return KB_OK;
 }
 
@@ -139,25 +148,86 @@ extern "C" int kb_sobol_fill_device(kb_ctx *ctx, int dim, uint64_t first_index, 
     return rc;
 }
 
+// Host-buffer fill.  The block is produced in chunks of about 32 MB into two alternating device buffers and leaves
+// through the copy stream while the next chunk is being generated; no allocation per call (the buffers belong to the
+// context and only grow), which matters for the service: it draws ONE point per suggestion (sample.go:39).  A
+// destination in pinned / registered host memory is written by the copies directly; a pageable one goes through two
+// pinned staging buffers, and a few host threads move each finished chunk on while the GPU works on the next ones.
+#define SOBOL_CHUNK_BYTES ((size_t)32 << 20)
+#define SOBOL_COPY_THREADS 4
+
+static void sobol_host_move(double *dst, const double *src, size_t bytes) {
+    if (bytes < ((size_t)4 << 20)) { memcpy(dst, src, bytes); return; }
+    std::thread th[SOBOL_COPY_THREADS - 1];
+    const size_t part = (bytes / SOBOL_COPY_THREADS) & ~(size_t)4095;
+    for (int t = 0; t < SOBOL_COPY_THREADS - 1; t++)
+        th[t] = std::thread([=] { memcpy((char *)dst + (size_t)t * part, (const char *)src + (size_t)t * part, part); });
+    const size_t done = (size_t)(SOBOL_COPY_THREADS - 1) * part;
+    memcpy((char *)dst + done, (const char *)src + done, bytes - done);
+    for (auto &t : th) t.join();
+}
+
 extern "C" int kb_sobol_fill(kb_ctx *ctx, int dim, uint64_t first_index, int64_t n_points, const double *low,
                              const double *high, double *out) {
     if (!ctx) return KB_ERR_INVALID;
-    double *d_out = nullptr;
-    {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        KbDeviceGuard g(ctx->device);
-        int rc = sobol_check(ctx, dim, first_index, n_points, low, high, out);
-        if (rc) return rc;
-        if (n_points == 0) return KB_OK;
-        KB_CUDA(ctx, cudaMalloc(&d_out, sizeof(double) * (size_t)n_points * dim));
-    }
-    int rc = kb_sobol_fill_device(ctx, dim, first_index, n_points, low, high, d_out, nullptr);
+    std::lock_guard<std::mutex> lk(ctx->mu);
     KbDeviceGuard g(ctx->device);
-    if (rc == KB_OK) {
-        cudaError_t e = cudaMemcpyAsync(out, d_out, sizeof(double) * (size_t)n_points * dim, cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) rc = kb_fail(ctx, KB_ERR_CUDA, "kb_sobol_fill: D2H: %s", cudaGetErrorString(e));
+    int rc = sobol_check(ctx, dim, first_index, n_points, low, high, out);
+    if (rc) return rc;
+    if (n_points == 0) return KB_OK;
+    if ((rc = sobol_tables(ctx))) return rc;
+    cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
+    const size_t row = sizeof(double) * (size_t)dim;
+    const int64_t chunk_pts = std::max<int64_t>(1, std::min<int64_t>(n_points, (int64_t)(SOBOL_CHUNK_BYTES / row)));
+    const size_t chunk_bytes = (size_t)chunk_pts * row;
+    cudaPointerAttributes attr;
+    const bool pinned_dst = cudaPointerGetAttributes(&attr, out) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();  // an unregistered pointer is not an error here
+    const size_t lh_bytes = low ? 2 * row : 0;
+    if (chunk_bytes + lh_bytes > ctx->sobol_buf_bytes) {
+        for (int i = 0; i < 2; i++) { cudaFree(ctx->d_sobol_buf[i]); ctx->d_sobol_buf[i] = nullptr; }
+        ctx->sobol_buf_bytes = 0;
+        const size_t want = std::max<size_t>(chunk_bytes + lh_bytes, (size_t)64 << 10);
+        for (int i = 0; i < 2; i++) KB_CUDA(ctx, cudaMalloc(&ctx->d_sobol_buf[i], want));
+        ctx->sobol_buf_bytes = want;
     }
-    cudaFree(d_out);
-    return rc;
+    if (!pinned_dst && chunk_bytes > ctx->sobol_pin_bytes) {
+        for (int i = 0; i < 2; i++) { if (ctx->h_sobol_pin[i]) cudaFreeHost(ctx->h_sobol_pin[i]); ctx->h_sobol_pin[i] = nullptr; }
+        ctx->sobol_pin_bytes = 0;
+        const size_t want = std::max<size_t>(chunk_bytes, (size_t)64 << 10);
+        for (int i = 0; i < 2; i++) KB_CUDA(ctx, cudaMallocHost(&ctx->h_sobol_pin[i], want));
+        ctx->sobol_pin_bytes = want;
+    }
+    const double *d_low = nullptr, *d_high = nullptr;
+    if (low) {  // the bounds ride behind the chunk area of buffer 0 (never overwritten by a chunk)
+        double *d_lh = (double *)((char *)ctx->d_sobol_buf[0] + (ctx->sobol_buf_bytes - lh_bytes));
+        KB_CUDA(ctx, cudaMemcpyAsync(d_lh, low, row, cudaMemcpyHostToDevice, s));
+        KB_CUDA(ctx, cudaMemcpyAsync(d_lh + dim, high, row, cudaMemcpyHostToDevice, s));
+        d_low = d_lh; d_high = d_lh + dim;
+    }
+    const int64_t n_chunks = (n_points + chunk_pts - 1) / chunk_pts;
+    auto drain = [&](int64_t k) -> cudaError_t {  // chunk k has left the device: move it on if it sits in staging
+        const int buf = (int)(k & 1);
+        cudaError_t e = cudaEventSynchronize(ctx->ev_h2d[buf]);
+        if (e == cudaSuccess && !pinned_dst) {
+            const int64_t off = k * chunk_pts, m = std::min<int64_t>(chunk_pts, n_points - off);
+            sobol_host_move(out + (size_t)off * dim, ctx->h_sobol_pin[buf], (size_t)m * row);
+        }
+        return e;
+    };
+    for (int64_t k = 0; k < n_chunks; k++) {
+        const int buf = (int)(k & 1);
+        const int64_t off = k * chunk_pts, m = std::min<int64_t>(chunk_pts, n_points - off);
+        if (k >= 2) KB_CUDA(ctx, drain(k - 2));  // device buffer and staging buffer `buf` are free again
+        if ((rc = sobol_launch(ctx, dim, first_index + (uint64_t)off, m, d_low, d_high, ctx->d_sobol_buf[buf], s))) return rc;
+        KB_CUDA(ctx, cudaEventRecord(ctx->ev_done[buf], s));
+        KB_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_done[buf], 0));
+        double *dst = pinned_dst ? out + (size_t)off * dim : ctx->h_sobol_pin[buf];
+        KB_CUDA(ctx, cudaMemcpyAsync(dst, ctx->d_sobol_buf[buf], (size_t)m * row, cudaMemcpyDeviceToHost, cs));
+        KB_CUDA(ctx, cudaEventRecord(ctx->ev_h2d[buf], cs));
+        // the fill of chunk k + 2 reuses this device buffer: it must wait for this copy
+        KB_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_h2d[buf], 0));
+    }
+    for (int64_t k = std::max<int64_t>(0, n_chunks - 2); k < n_chunks; k++) KB_CUDA(ctx, drain(k));
+    return KB_OK;
 }
