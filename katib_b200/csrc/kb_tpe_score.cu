@@ -1631,9 +1631,13 @@ static int tpe_run_host(kb_ctx *ctx, int64_t n_cand, const double *cand, int64_t
     if (rc) return rc;
     if (select && (rc = tpe_reset_selection(ctx, s))) return rc;
     const int64_t cap = std::min<int64_t>(ctx->chunk_cap, rows);
+    // The first copy has nothing to hide behind: start with a small chunk (64 Ki rows) and double up to the full
+    // chunk size, so that the exposed H2D time is that of the small one
+    int64_t cur = std::min<int64_t>(cap, 65536);
     int buf = 0;
-    for (int64_t off = 0; off < n_cand; off += cap, buf ^= 1) {
-        const int n = (int)(n_cand - off < cap ? n_cand - off : cap);
+    for (int64_t off = 0, n64 = 0; off < n_cand; off += n64, buf ^= 1, cur = std::min<int64_t>(cap, cur * 2)) {
+        n64 = std::min<int64_t>(cur, n_cand - off);
+        const int n = (int)n64;
         KB_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_done[buf], 0));  // landing buffer free again
         KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cand_chunk[buf], cand + (size_t)off * D, sizeof(double) * (size_t)n * D,
                                      cudaMemcpyHostToDevice, cs));
