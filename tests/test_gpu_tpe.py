@@ -203,6 +203,45 @@ def test_config5_shape_reduced(ctx):
     assert list(idx) == best
 
 
+@pytest.mark.slow
+@pytest.mark.skipif(os.environ.get("KB_SLOW") != "1", reason="about two minutes of CPU-oracle time on 24 cores: KB_SLOW=1")
+def test_config5_shape_1Mi_rows():
+    """the 1 Mi-row subset of BASELINE configs[4] against the oracle -- every score of all 50
+    parameters within 1e-5, every winner identical.  The oracle runs on all host threads (the C port releases the GIL).
+    The same rows then go through kb_tpe_score_error_device: the FP64 side computed on the GPU must tell the same story."""
+    import threading
+    import bench
+    kinds, lows, highs, steps, nch = bench.workload_space()
+    vals, loss = bench.workload_history(kinds, lows, highs, steps, nch)
+    ctx = kb.Context(0)
+    ctx.space_set(kinds, lows, highs, steps, nch)
+    ctx.tpe_set_history(vals, loss)
+    rng = np.random.Generator(np.random.PCG64(55))
+    sp = dict(kinds=kinds, lows=lows, highs=highs, steps=steps, nch=nch)
+    n = 1 << 20
+    cand = sample_candidates(rng, n, sp, vals)
+    got = ctx.tpe_scores(cand)
+    idx = ctx.tpe_score_select(cand)[0]
+    parts = np.array_split(np.arange(n), os.cpu_count() or 8)
+    ref = np.empty_like(cand)
+
+    def work(p):
+        ref[p] = oracle_scores(kinds, lows, highs, steps, nch, vals, loss, cand[p])[0]
+    ths = [threading.Thread(target=work, args=(p,)) for p in parts]
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    errs = np.array([rel_err(got[:, d], ref[:, d]) for d in range(len(kinds))])
+    print("config5-shape, 2^20 rows: max rel err cont %.2e quant %.2e cat %.2e" % (errs[:20].max(), errs[20:30].max(), errs[30:].max()))
+    assert errs.max() < TOL, errs
+    assert list(idx) == [int(np.argmax(ref[:, d])) for d in range(len(kinds))]
+    import torch
+    t = torch.from_numpy(cand).to("cuda:0")
+    dev_err = ctx.tpe_score_error_device(n, t.data_ptr())
+    print("same rows, FP64 side on the device: cont %.2e quant %.2e" % (dev_err[:20].max(), dev_err[20:30].max()))
+    assert dev_err.max() < TOL and np.all(np.abs(dev_err[:30] - errs[:30]) < 2e-7)
+    ctx.close()
+
+
 def test_multi_chunk_host_path_and_offsets(monkeypatch):
     """2.5 Mi candidates cross the chunk boundary three times (double-buffered H2D; chunks of 2^20 rows forced on a
     fresh context, the default is 2^22): winners and indices vs the oracle."""
