@@ -79,6 +79,8 @@ extern "C" int kb_destroy(kb_ctx *ctx) {
             if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
         }
         if (ctx->ev_build) cudaEventDestroy(ctx->ev_build);
+        if (ctx->ev_up) cudaEventDestroy(ctx->ev_up);
+        if (ctx->h_up) cudaFreeHost(ctx->h_up);
         prof_drain(ctx);
         for (auto e : ctx->prof_pool) cudaEventDestroy(e);
         if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -191,6 +193,7 @@ extern "C" int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, cons
     ctx->d_dims = nullptr; ctx->d_cont_dims = ctx->d_quant_dims = ctx->d_cat_dims = nullptr;
     ctx->D = n_params;
     ctx->h_dims = dims;
+    ctx->h_dims_sent.clear();  // d_dims is a new allocation
     ctx->cont_dims = cont; ctx->quant_dims = quant; ctx->cat_dims = cat;
     ctx->n_cont = (int)cont.size(); ctx->n_quant = (int)quant.size(); ctx->n_cat = (int)cat.size();
     ctx->n_numeric = numeric;

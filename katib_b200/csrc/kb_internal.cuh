@@ -135,9 +135,17 @@ struct kb_ctx {
     double *d_sort_keys = nullptr;   // scratch for the bitonic sorts
     uint32_t *d_sort_idx = nullptr;
     int64_t sort_cap = 0;
+    double *d_small_keys = nullptr;  // per-CTA scratch of the single-launch build (small histories)
+    uint32_t *d_small_idx = nullptr;
+    int32_t *d_small_pos = nullptr;
+    int64_t small_cap = 0;
     double *d_tabmem = nullptr;      // arena behind the KbDim table pointers
     size_t tabmem_bytes = 0;
     bool history_ready = false;
+    void *h_up = nullptr;            // pinned staging of the history upload (grow-only) and the event behind its copies
+    size_t up_bytes = 0;
+    cudaEvent_t ev_up = nullptr;
+    std::vector<char> h_dims_sent;   // the descriptor table as last uploaded (d_dims is rewritten only when it differs)
     bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
     bool tpe_prune = false;          // KB_OPT_PRUNE_FAR
     bool quant_attr_set = false;     // dynamic shared-memory limit of the quantised score kernels raised

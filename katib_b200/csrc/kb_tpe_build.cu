@@ -24,7 +24,34 @@ static int next_pow2(int64_t v) {
 static inline int pad_to(int v, int m) { return (v + m - 1) / m * m; }
 
 // ---- bitonic sort of (key, idx) pairs by (key asc, idx asc), one CTA, arrays in global memory -------------
+#define SORT_SMEM_MAX 1024
 __device__ void bitonic_sort_pairs(double *keys, uint32_t *idx, int npad) {
+    // small arrays (the GetSuggestions-latency shapes) are sorted in shared memory: same network, same result, but a
+    // stage costs a barrier instead of a round trip to L2
+    __shared__ double s_keys[SORT_SMEM_MAX];
+    __shared__ uint32_t s_idx[SORT_SMEM_MAX];
+    if (npad <= SORT_SMEM_MAX) {
+        for (int i = threadIdx.x; i < npad; i += blockDim.x) { s_keys[i] = keys[i]; s_idx[i] = idx[i]; }
+        __syncthreads();
+        for (int k = 2; k <= npad; k <<= 1) {
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+                    int ixj = i ^ j;
+                    if (ixj > i) {
+                        double a = s_keys[i], b = s_keys[ixj];
+                        uint32_t ia = s_idx[i], ib = s_idx[ixj];
+                        bool gt = (a > b) || (a == b && ia > ib);
+                        bool up = (i & k) == 0;
+                        if (gt == up) { s_keys[i] = b; s_keys[ixj] = a; s_idx[i] = ib; s_idx[ixj] = ia; }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        for (int i = threadIdx.x; i < npad; i += blockDim.x) { keys[i] = s_keys[i]; idx[i] = s_idx[i]; }
+        __syncthreads();
+        return;
+    }
     for (int k = 2; k <= npad; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int i = threadIdx.x; i < npad; i += blockDim.x) {
@@ -59,8 +86,7 @@ __device__ __forceinline__ double tpe_ramp(int pos, int m) {
 }
 
 // ---- split: rank trials by loss; pos[0][i] / pos[1][i] = position of trial i inside below / above --------
-__global__ void __launch_bounds__(BUILD_THREADS)
-split_kernel(const double *__restrict__ loss, int n, int npad, double *keys, uint32_t *idx, int32_t *pos) {
+__device__ void split_body(const double *__restrict__ loss, int n, int npad, double *keys, uint32_t *idx, int32_t *pos) {
     __shared__ int s_cnt[BUILD_THREADS];
     for (int i = threadIdx.x; i < npad; i += blockDim.x) {
         keys[i] = i < n ? loss[i] : INFINITY;
@@ -97,21 +123,20 @@ split_kernel(const double *__restrict__ loss, int n, int npad, double *keys, uin
     }
 }
 
-// ---- Parzen estimator of one (numeric parameter, side) ---------------------------------------------------
 __global__ void __launch_bounds__(BUILD_THREADS)
-parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ values, int n, int D, int nb,
-              const int32_t *__restrict__ pos, int npad_stride, double *keys_all, uint32_t *idx_all, int merge) {
+split_kernel(const double *__restrict__ loss, int n, int npad, double *keys, uint32_t *idx, int32_t *pos) {
+    split_body(loss, n, npad, keys, idx, pos);
+}
+
+// ---- Parzen estimator of one (numeric parameter, side) ---------------------------------------------------
+__device__ void parzen_body(KbDim &dm, int d, int side, const double *__restrict__ values, int n, int D, int nb,
+                            const int32_t *__restrict__ pos, double *keys, uint32_t *idx, int merge) {
     __shared__ double s_red[BUILD_THREADS];
     __shared__ double s_scalar[2];
     __shared__ int s_int[BUILD_THREADS];
-    const int slot = blockIdx.x, side = blockIdx.y;
-    const int d = numeric_dims[slot];
-    KbDim &dm = dims[d];
     const int m = side == 0 ? nb : n - nb;  // observations on this side
     const int K0 = m + 1;  // components before the optional merge
     int K = K0;
-    double *keys = keys_all + ((size_t)slot * 2 + side) * npad_stride;
-    uint32_t *idx = idx_all + ((size_t)slot * 2 + side) * npad_stride;
     int npad = 2;  // this side's own power of two (>= K): the below side holds at most 26 entries
     while (npad < K) npad <<= 1;
     const double low = dm.lo, high = dm.hi, shift = dm.shift;
@@ -503,15 +528,22 @@ parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ v
     }
 }
 
+__global__ void __launch_bounds__(BUILD_THREADS)
+parzen_kernel(KbDim *dims, const int *numeric_dims, const double *__restrict__ values, int n, int D, int nb,
+              const int32_t *__restrict__ pos, int npad_stride, double *keys_all, uint32_t *idx_all, int merge) {
+    const int slot = blockIdx.x, side = blockIdx.y;
+    const int d = numeric_dims[slot];
+    parzen_body(dims[d], d, side, values, n, D, nb, pos, keys_all + ((size_t)slot * 2 + side) * npad_stride,
+                idx_all + ((size_t)slot * 2 + side) * npad_stride, merge);
+}
+
 // ---- categorical parameters: weighted bincount (trial order) + prior weight, log ratio, ranks ------------
-#define CAT_CHUNK 4096
-__global__ void categorical_kernel(KbDim *dims, const int *cat_dims, const double *__restrict__ values, int n, int D,
-                                   int nb, const int32_t *__restrict__ pos) {
+#define CAT_CHUNK 2048
+__device__ void categorical_body(KbDim &dm, int d, const double *__restrict__ values, int n, int D, int nb,
+                                 const int32_t *__restrict__ pos) {
     __shared__ double s_sum[2];
     __shared__ int s_pos[CAT_CHUNK];
     __shared__ unsigned short s_cat[CAT_CHUNK];
-    const int d = cat_dims[blockIdx.x];
-    KbDim &dm = dims[d];
     const int C = dm.n_choices;
     for (int side = 0; side < 2; side++) {
         const int m = side == 0 ? nb : n - nb;
@@ -555,11 +587,38 @@ __global__ void categorical_kernel(KbDim *dims, const int *cat_dims, const doubl
     }
     if (threadIdx.x == 0) { dm.K[0] = dm.K[1] = C; dm.Kpad[0] = dm.Kpad[1] = C; }
 }
+__global__ void categorical_kernel(KbDim *dims, const int *cat_dims, const double *__restrict__ values, int n, int D,
+                                   int nb, const int32_t *__restrict__ pos) {
+    const int d = cat_dims[blockIdx.x];
+    categorical_body(dims[d], d, values, n, D, nb, pos);
+}
+
+// ---- small histories (the GetSuggestions-latency shapes): ONE launch builds everything.  CTA (d, side) ranks the
+// trials by loss for itself -- the split is a 128-element sort there, cheaper to repeat than to wait for -- and goes
+// straight on to its estimator (numeric: one side each; categorical: CTA (d, 0) does both sides).
+__global__ void __launch_bounds__(BUILD_THREADS)
+tpe_build_small_kernel(KbDim *dims, const double *__restrict__ values, const double *__restrict__ loss, int n, int D, int nb,
+                       int npad, double *keys_all, uint32_t *idx_all, int32_t *pos_all, int merge) {
+    const int d = blockIdx.x, side = blockIdx.y;
+    KbDim &dm = dims[d];
+    if (dm.kind == KB_CATEGORICAL && side == 1) return;
+    const size_t me = (size_t)d * 2 + side;
+    double *keys = keys_all + me * npad;
+    uint32_t *idx = idx_all + me * npad;
+    int32_t *pos = pos_all + me * 2 * (size_t)(n > 0 ? n : 1);
+    split_body(loss, n, npad, keys, idx, pos);
+    __syncthreads();
+    if (dm.kind == KB_CATEGORICAL) categorical_body(dm, d, values, n, D, nb, pos);
+    else parzen_body(dm, d, side, values, n, D, nb, pos, keys, idx, merge);
+}
+#define KB_BUILD_SMALL_MAX 1000  // trials up to which the single-launch build is used
 
 // ---- host side -----------------------------------------------------------------------------------------------
 int kb_tpe_free_history(kb_ctx *ctx) {
     cudaFree(ctx->d_values); cudaFree(ctx->d_loss); cudaFree(ctx->d_pos);
     cudaFree(ctx->d_sort_keys); cudaFree(ctx->d_sort_idx); cudaFree(ctx->d_tabmem);
+    cudaFree(ctx->d_small_keys); cudaFree(ctx->d_small_idx); cudaFree(ctx->d_small_pos);
+    ctx->d_small_keys = nullptr; ctx->d_small_idx = nullptr; ctx->d_small_pos = nullptr; ctx->small_cap = 0;
     ctx->d_values = ctx->d_loss = nullptr; ctx->d_pos = nullptr;
     ctx->d_sort_keys = nullptr; ctx->d_sort_idx = nullptr; ctx->d_tabmem = nullptr;
     ctx->hist_cap = 0; ctx->sort_cap = 0; ctx->tabmem_bytes = 0;
@@ -645,13 +704,64 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
             }
         }
     }
-    KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_dims, ctx->h_dims.data(), sizeof(KbDim) * (size_t)D, cudaMemcpyHostToDevice, s));
-    if (n_add > 0) {
-        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_values + (size_t)keep * D, values, sizeof(double) * (size_t)n_add * D,
-                                     cudaMemcpyHostToDevice, s));
-        KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_loss + keep, loss, sizeof(double) * (size_t)n_add, cudaMemcpyHostToDevice, s));
+    // Uploads go through a pinned staging buffer of the context: a copy from pageable memory costs the driver a
+    // staging pass and a synchronisation per call (three of them were a third of the GetSuggestions latency); from
+    // pinned memory the three copies are plain asynchronous DMA.  The descriptor table is sent only when it changed
+    // (the table pointers move when the history crosses a multiple of 32 rows).
+    {
+        const size_t dims_b = sizeof(KbDim) * (size_t)D, val_b = sizeof(double) * (size_t)n_add * D, loss_b = sizeof(double) * (size_t)n_add;
+        // compared without K / Kpad: the host mirrors them after every build, the device copy is written by the kernels
+        std::vector<KbDim> canon(ctx->h_dims);
+        for (KbDim &k : canon) { k.K[0] = k.K[1] = 0; k.Kpad[0] = k.Kpad[1] = 0; }
+        const bool dims_changed = ctx->h_dims_sent.size() != dims_b || memcmp(ctx->h_dims_sent.data(), canon.data(), dims_b) != 0;
+        const size_t need = dims_b + val_b + loss_b;
+        if (need <= ((size_t)4 << 20)) {
+            if (need > ctx->up_bytes) {
+                if (ctx->h_up) { cudaStreamSynchronize(s); cudaFreeHost(ctx->h_up); ctx->h_up = nullptr; ctx->up_bytes = 0; }
+                const size_t want = std::max<size_t>(need * 2, (size_t)64 << 10);
+                KB_CUDA(ctx, cudaMallocHost(&ctx->h_up, want));
+                ctx->up_bytes = want;
+                if (!ctx->ev_up) KB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_up, cudaEventDisableTiming));
+            } else if (ctx->ev_up) {
+                KB_CUDA(ctx, cudaEventSynchronize(ctx->ev_up));  // the previous call's copies have left the buffer
+            }
+            char *hp = (char *)ctx->h_up;
+            if (dims_changed) {
+                memcpy(hp, canon.data(), dims_b);
+                KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_dims, hp, dims_b, cudaMemcpyHostToDevice, s));
+            }
+            if (n_add > 0) {
+                memcpy(hp + dims_b, values, val_b);
+                memcpy(hp + dims_b + val_b, loss, loss_b);
+                KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_values + (size_t)keep * D, hp + dims_b, val_b, cudaMemcpyHostToDevice, s));
+                KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_loss + keep, hp + dims_b + val_b, loss_b, cudaMemcpyHostToDevice, s));
+            }
+            KB_CUDA(ctx, cudaEventRecord(ctx->ev_up, s));
+        } else {  // a large history: straight from the caller's memory
+            if (dims_changed) KB_CUDA(ctx, cudaMemcpy(ctx->d_dims, canon.data(), dims_b, cudaMemcpyHostToDevice));  // canon is a local
+            KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_values + (size_t)keep * D, values, val_b, cudaMemcpyHostToDevice, s));
+            KB_CUDA(ctx, cudaMemcpyAsync(ctx->d_loss + keep, loss, loss_b, cudaMemcpyHostToDevice, s));
+        }
+        if (dims_changed) ctx->h_dims_sent.assign((const char *)canon.data(), (const char *)canon.data() + dims_b);
     }
     const int nb = [&] { int a = (int)ceil(0.1 * (double)n); return a > 25 ? 25 : a; }();
+    static const bool small_ok = [] { const char *e = getenv("KB_BUILD_SMALL"); return !(e && e[0] == '0'); }();
+    if (n <= KB_BUILD_SMALL_MAX && small_ok) {
+        const size_t blocks = (size_t)D * 2;
+        if ((int64_t)(blocks * npad) > ctx->small_cap) {
+            cudaFree(ctx->d_small_keys); cudaFree(ctx->d_small_idx); cudaFree(ctx->d_small_pos);
+            ctx->d_small_keys = nullptr; ctx->d_small_idx = nullptr; ctx->d_small_pos = nullptr; ctx->small_cap = 0;
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_small_keys, sizeof(double) * blocks * npad));
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_small_idx, sizeof(uint32_t) * blocks * npad));
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_small_pos, sizeof(int32_t) * blocks * 2 * npad));  // npad > n
+            ctx->small_cap = (int64_t)(blocks * npad);
+        }
+        KbProf pf(ctx, 5, s);
+        tpe_build_small_kernel<<<dim3((unsigned)D, 2), BUILD_THREADS, 0, s>>>(ctx->d_dims, ctx->d_values, ctx->d_loss, n, D, nb, npad,
+                                                                             ctx->d_small_keys, ctx->d_small_idx, ctx->d_small_pos,
+                                                                             ctx->tpe_merge ? 1 : 0);
+        KB_LAUNCH_CHECK(ctx);
+    } else {
     split_kernel<<<1, BUILD_THREADS, 0, s>>>(ctx->d_loss, n, npad, ctx->d_sort_keys, ctx->d_sort_idx, ctx->d_pos);
     KB_LAUNCH_CHECK(ctx);
     if (ctx->n_numeric > 0) {
@@ -670,6 +780,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
     if (ctx->n_cat > 0) {
         categorical_kernel<<<ctx->n_cat, 128, 0, s>>>(ctx->d_dims, ctx->d_cat_dims, ctx->d_values, n, D, nb, ctx->d_pos);
         KB_LAUNCH_CHECK(ctx);
+    }
     }
     // K / Kpad are known on the host (n_side + 1); p_accept and L stay on the device (kb_tpe_get_parzen fetches them),
     // so the call returns without synchronising: on the context's stream the kernels above are simply ordered before
