@@ -340,6 +340,23 @@ def main():
         else:
             e2e = {"value": None, "unit": "candidates/s", "note": pinned_note}
 
+    # ---- secondary: the whole of tpe.Sampler.Sample at this size -- kb_tpe_suggest draws its 2^cand candidates from l(x)
+    # on the device (chunk by chunk, straight into the staged columns: no candidate matrix), scores and selects; with
+    # N ranks every rank draws and scores its index range of the one stream.  Against `value` this shows what the
+    # sampling costs.
+    suggest = None
+    if os.environ.get("KB_BENCH_SUGGEST", "1") == "1":
+        free0 = torch.cuda.mem_get_info(dev)[0]
+        step_sug = lambda: ctx.tpe_suggest(n_total, 4242)
+        for _ in range(min(2, args.warmup)):
+            out_sug = step_sug()
+        ms_s, wall_s, out_sug = timed(step_sug, args.steps)
+        suggest = {"value": n_total * args.steps / (ms_s * 1e-3), "unit": "candidates/s (drawn, scored, selected)",
+                   "ms_per_step": ms_s / args.steps, "extra_device_memory_bytes": int(max(0, free0 - torch.cuda.mem_get_info(dev)[0])),
+                   "suggestion_head": [float(x) for x in out_sug[:4]],
+                   "note": "kb_tpe_suggest(n_ei_candidates = the whole set): Philox draw from the below mixture fused into the "
+                           "staging kernel, same scoring kernels; the candidates are never stored"}
+
     # ---- secondary: the same step with KB_OPT_MERGE_DUPLICATES (what kb_service_* runs with).  Reported beside the
     # headline, never as it: the headline and the roofline count every one of the reference's n+1 components.
     merged = None
@@ -511,7 +528,7 @@ def main():
            "cpu_baseline": {"value": cpu_v, "unit": "candidates/s", "cores": cores, "kind": "port",
                             "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history, {cpu_dt:.1f} s, "
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
-           "merged_duplicates": merged, "pruned": pruned, "latency": latency,
+           "suggest_whole_set": suggest, "merged_duplicates": merged, "pruned": pruned, "latency": latency,
            "winners_vs_oracle": winners_vs_oracle, "score_error_max": score_error, "secondary": secondary,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
     print(json.dumps(out), flush=True)
