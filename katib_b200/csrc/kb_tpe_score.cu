@@ -307,15 +307,18 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
 // loop (16 ex2 / clk / SM against 128 FP32 lanes): of every 16 components, those whose bit is set in SC_SW_MASK take
 // their 2^e from kb_ex2_fma2 instead, which moves that share of the exponentials onto the otherwise half-idle FMA
 // pipe.  Every (candidate, component) pair is still evaluated.
-// Masks for 0, 2, 3 and 4 of every 16 components; 3/16 balances the two pipes on paper (XU 13 cycles, FMA 13 cycles per
-// pair-component); KB_CONT_SW = 0 | 2 | 3 | 4 picks another at run time (measurement only).
+// Masks for 0, 1, 2, 3 and 4 of every 16 components.  On paper 3/16 balances the two pipes (XU 13 cycles, FMA 13 cycles
+// per pair-component); measured on B200 at 2^24 candidates x 20 parameters x 10 002 components: 0 -> 2313 ms, 1 -> 2258 ms,
+// 2 -> 2338 ms, 3 -> 2427 ms, 4 -> 2535 ms (ncu at 1/16: XU 89.5 %, FMA pipe 69 %, issue 53 %; the polynomial's dependent
+// chain and the MIO queue stop the two pipes from overlapping further).  1/16 is the default; KB_CONT_SW = 0..4 picks
+// another at run time (measurement only).
 #define SC_SW_MASK_0 0x0000u
 #define SC_SW_MASK_1 0x0100u
 #define SC_SW_MASK_2 0x0404u
 #define SC_SW_MASK_3 0x1084u
 #define SC_SW_MASK_4 0x4444u
 #ifndef SC_SW_DEFAULT
-#define SC_SW_DEFAULT 0
+#define SC_SW_DEFAULT 1
 #endif
 template <unsigned SC_SW_MASK>
 __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const float2 (&xh)[SC_R / 2],
@@ -1508,7 +1511,7 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
                                                               ctx->d_stage_sorted, ctx->d_perm);
         KB_LAUNCH_CHECK(ctx);
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
-        tpe_score_cont_pruned_kernel<SC_SW_MASK_3><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
+        tpe_score_cont_pruned_kernel<SC_SW_MASK_1><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
                                                                  ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score,
                                                                  ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
@@ -1521,10 +1524,10 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,           \
                                                                 sc->d_tie_score, ctx->tie_slots, d_cand, d_scores)
         if (sw == 0) KB_CONT_LAUNCH(SC_SW_MASK_0);
-        else if (sw == 1) KB_CONT_LAUNCH(SC_SW_MASK_1);
         else if (sw == 2) KB_CONT_LAUNCH(SC_SW_MASK_2);
         else if (sw == 4) KB_CONT_LAUNCH(SC_SW_MASK_4);
-        else KB_CONT_LAUNCH(SC_SW_MASK_3);
+        else if (sw == 3) KB_CONT_LAUNCH(SC_SW_MASK_3);
+        else KB_CONT_LAUNCH(SC_SW_MASK_1);
 #undef KB_CONT_LAUNCH
         KB_LAUNCH_CHECK(ctx);
     }
