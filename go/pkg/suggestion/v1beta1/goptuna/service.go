@@ -39,8 +39,8 @@ import (
 )
 
 // DevicesEnv lists the CUDA devices one service instance drives, e.g. "0" or "0,1,2,3,4,5,6,7".
-// Unset = device 0.  With more than one device the candidate set of a TPE request is sharded over them and one
-// NCCL collective picks the winners (kb_service_create_multi).
+// Unset = device 0.  With more than one device the candidate set of a large TPE request is sharded over them and the
+// per-GPU winners are merged inside the library (kb_service_create_multi).
 const DevicesEnv = "KATIB_B200_DEVICES"
 
 // SuggestionService replaces the struct at service.go:47-52: the study, the search space and the trial mapping all

@@ -227,11 +227,13 @@ typedef struct kb_service kb_service;
 int kb_service_create(int device, kb_service **out);
 /* The same service over several GPUs of this machine (devices[0 .. n_devices), distinct).  The controller talks to ONE
  * service process per experiment (composer.go:72-146; main.go:43-57), so the GPUs are driven from inside it: one
- * kb_ctx and one host thread per GPU, one NCCL communicator owned by the service.  Requests are answered by devices[0]
- * alone, except TPE requests whose n_ei_candidates setting is at least 65536: then every GPU draws and scores its
- * contiguous index range of the candidate stream and one collective per suggestion merges the winners -- the reply is
- * the one a single-GPU service gives for the same request.  Contexts and communicator are made at the first
- * GetSuggestions, like the reference's study (service.go:153-171). */
+ * kb_ctx and one host thread per GPU.  Requests are answered by devices[0] alone, except TPE requests whose
+ * n_ei_candidates setting is at least 65536: then every GPU draws and scores its contiguous index range of the
+ * candidate stream and the per-GPU winners (D x 24 bytes each) are merged on the host by the argmax rule (best score,
+ * lowest candidate index) -- the reply is the one a single-GPU service gives for the same request.  Inside one
+ * process no NCCL communicator is used (the winners already share an address space); one process per GPU
+ * (kb_comm_init) is the deployment that merges over NCCL.  Contexts are made at the first GetSuggestions, like the
+ * reference's study (service.go:153-171). */
 int kb_service_create_multi(int n_devices, const int *devices, kb_service **out);
 int kb_service_destroy(kb_service *svc);
 /* SuggestionService.GetSuggestions (service.go:54-93).  *reply points into memory owned by svc, valid until the

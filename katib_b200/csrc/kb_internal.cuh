@@ -243,6 +243,8 @@ int kb_cmaes_free(kb_ctx *ctx);
 int kb_comm_free(kb_ctx *ctx);
 int kb_comm_allgather(kb_ctx *ctx, const void *send, void *recv, size_t bytes, cudaStream_t s);
 int kb_comm_allreduce_sum_f64(kb_ctx *ctx, double *buf, size_t count, cudaStream_t s);
+int kb_tpe_suggest_range(kb_ctx *ctx, uint64_t seed, int64_t first, int64_t count, int64_t *out_index, double *out_value,
+                         double *out_score);
 
 // ---- device helpers ------------------------------------------------------------------------------------
 #ifdef __CUDACC__

@@ -283,9 +283,12 @@ struct kb_service {
     std::mutex mu;
     int device = 0;
     kb_ctx *ctx = nullptr;
-    // kb_service_create_multi: the other GPUs of this service.  ctx (on devices[0]) is rank 0 of one NCCL communicator
-    // over all of them and the only context that serves CMA-ES, Sobol, random and small TPE requests; the peers hold
-    // replicas of the search space and the TPE history and join in when a TPE request is large enough to shard.
+    // kb_service_create_multi: the other GPUs of this service.  ctx (on devices[0]) is the only context that serves
+    // CMA-ES, Sobol, random and small TPE requests; the peers hold replicas of the search space and the TPE history and
+    // join in when a TPE request is large enough to shard.  All of them live in this one process, so their winners are
+    // merged on the host (kb_tpe_suggest_range): no communicator is needed, and none is made -- NCCL kernels of several
+    // GPUs driven from one process can deadlock against a cudaMalloc on another thread, a hazard a merge of D x 24
+    // bytes per GPU does not justify.  (One process per GPU -- bench.py, tests/mp_tpe_sharded.py -- uses NCCL.)
     std::vector<int> devices;
     std::vector<kb_ctx *> peers;  // ranks 1 .. n-1
     bool initialised = false;
@@ -495,8 +498,8 @@ static Status engine_error(kb_service *s, const char *what) {
     return fail(GRPC_INTERNAL, std::string(what) + ": " + kb_last_error(s->ctx));
 }
 
-// f(rank, ctx) on every context of the service, one host thread per GPU: calls that contain a collective block until
-// all ranks have entered it.  Returns the first non-zero code (and that context, for its error text).
+// f(rank, ctx) on every context of the service, one host thread per GPU so that the GPUs work at the same time.
+// Returns the first non-zero code (and that context, for its error text).
 template <class F>
 static int on_all_contexts(kb_service *s, F f, kb_ctx **failed = nullptr) {
     const size_t n = 1 + s->peers.size();
@@ -701,14 +704,26 @@ static Status SampleNext(kb_service *s, std::vector<KV> &assignments) {
         if (st.code) return st;
         const uint64_t seed = mix_seed((uint64_t)s->algo.seed, s->draw_counter++);
         if (!s->peers.empty() && s->algo.n_ei >= KB_SERVICE_SHARD_MIN) {
-            // a large candidate set: every GPU draws and scores its index range of the one Philox stream, one NCCL
-            // collective merges the winners (kb_tpe_suggest with a communicator); all ranks return the same values
-            std::vector<std::vector<double>> vr(1 + s->peers.size(), std::vector<double>(D, 0.0));
+            // a large candidate set: every GPU draws and scores its index range of the one Philox stream (shard_range of
+            // katib_b200/sharding.py); the per-GPU winners are merged here by tpe.Sampler's argmax rule -- best score,
+            // lowest candidate index on ties -- which makes the answer that of one GPU scoring the whole set
+            const size_t W = 1 + s->peers.size();
+            const int64_t n_ei = s->algo.n_ei, base = n_ei / (int64_t)W, extra = n_ei % (int64_t)W;
+            std::vector<std::vector<int64_t>> ir(W, std::vector<int64_t>(D, -1));
+            std::vector<std::vector<double>> vr(W, std::vector<double>(D, 0.0)), sr(W, std::vector<double>(D, 0.0));
             kb_ctx *bad = nullptr;
-            const int64_t n_ei = s->algo.n_ei;
-            if (on_all_contexts(s, [&](int r, kb_ctx *c) { return kb_tpe_suggest(c, n_ei, seed, vr[(size_t)r].data()); }, &bad))
+            if (on_all_contexts(s, [&](int r, kb_ctx *c) {
+                    const int64_t first = r * base + std::min<int64_t>(r, extra), count = base + (r < extra ? 1 : 0);
+                    return kb_tpe_suggest_range(c, seed, first, count, ir[(size_t)r].data(), vr[(size_t)r].data(), sr[(size_t)r].data());
+                }, &bad))
                 return fail(GRPC_INTERNAL, std::string("kb_tpe_suggest: ") + kb_last_error(bad));
-            v = vr[0];
+            for (size_t d = 0; d < D; d++) {
+                int64_t bi = -1; double bs = 0.0;
+                for (size_t r = 0; r < W; r++) {
+                    if (ir[r][d] < 0) continue;
+                    if (bi < 0 || sr[r][d] > bs || (sr[r][d] == bs && ir[r][d] < bi)) { bi = ir[r][d]; bs = sr[r][d]; v[d] = vr[r][d]; }
+                }
+            }
         } else if (kb_tpe_suggest(s->ctx, s->algo.n_ei, seed, v.data()))
             return engine_error(s, "kb_tpe_suggest");
     } else if (algo == "sobol") {
@@ -766,7 +781,7 @@ static Status InitAtFirstRun(kb_service *s, const ExperimentMsg &e) {
     if (sp.empty()) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + "empty search space");
     if (!s->ctx && kb_create(s->device, &s->ctx)) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(nullptr));
     if (s->devices.size() > 1 && s->peers.empty()) {
-        // one context per further GPU, then one communicator over all of them (rank = position in the device list)
+        // one context per further GPU (rank = position in the device list)
         for (size_t r = 1; r < s->devices.size(); r++) {
             kb_ctx *c = nullptr;
             if (kb_create(s->devices[r], &c)) {
@@ -776,12 +791,6 @@ static Status InitAtFirstRun(kb_service *s, const ExperimentMsg &e) {
             }
             s->peers.push_back(c);
         }
-        char uid[128];
-        if (kb_comm_unique_id(uid)) return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(nullptr));
-        const int world = (int)s->devices.size();
-        kb_ctx *bad = nullptr;
-        if (on_all_contexts(s, [&](int r, kb_ctx *c) { return kb_comm_init(c, world, r, uid); }, &bad))
-            return fail(GRPC_INTERNAL, std::string(kFailedStudy) + kb_last_error(bad));
     }
     const size_t D = sp.size();
     std::vector<int32_t> kind(D), nch(D);
@@ -845,9 +854,8 @@ extern "C" int kb_service_create_multi(int n_devices, const int *devices, kb_ser
 }
 extern "C" int kb_service_destroy(kb_service *s) {
     if (!s) return KB_OK;
-    // the communicator is torn down on all ranks together (ncclCommDestroy of one rank may wait for the others)
-    if (!s->peers.empty()) on_all_contexts(s, [](int, kb_ctx *c) { return kb_destroy(c); });
-    else if (s->ctx) kb_destroy(s->ctx);
+    for (kb_ctx *p : s->peers) kb_destroy(p);
+    if (s->ctx) kb_destroy(s->ctx);
     delete s;
     return KB_OK;
 }

@@ -1724,6 +1724,9 @@ extern "C" int kb_tpe_score_select_device(kb_ctx *ctx, int64_t n_cand, const dou
 
 // Full tpe.Sampler.Sample for every parameter: draw on the device (kb_tpe_sample.cu), score, select.
 
+static int tpe_suggest_range(kb_ctx *ctx, uint64_t seed, int64_t first, int64_t count, bool collective, int64_t *out_index,
+                             double *out_value, double *out_score);
+
 extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t seed, double *out_value) {
     if (!ctx) return KB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -1769,6 +1772,13 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
         first = rank * base + std::min<int64_t>(rank, extra);
         count = base + (rank < extra ? 1 : 0);
     }
+    return tpe_suggest_range(ctx, seed, first, count, sharded, nullptr, out_value, nullptr);
+}
+
+// Candidates [first, first + count) of the Philox stream `seed`, drawn into the staged columns, scored, selected.
+static int tpe_suggest_range(kb_ctx *ctx, uint64_t seed, int64_t first, int64_t count, bool collective, int64_t *out_index,
+                             double *out_value, double *out_score) {
+    cudaStream_t s = ctx->stream;
     const int64_t rows = std::max<int64_t>(1, std::min<int64_t>(count, KB_CHUNK_ROWS));
     int rc = KB_OK;
     for (int attempt = 0; !rc; attempt++) {
@@ -1779,11 +1789,24 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
             const int m = (int)(count - off < cap ? count - off : cap);
             rc = tpe_launch_chunk(ctx, nullptr, m, first + off, off, true, nullptr, s, seed);
         }
-        if (!rc) rc = tpe_finish_selection(ctx, first, nullptr, out_value, nullptr, s, sharded);
+        if (!rc) rc = tpe_finish_selection(ctx, first, out_index, out_value, out_score, s, collective);
         if (!tpe_retry_overflow(ctx, rc, attempt)) break;
         rc = KB_OK;
     }
     return rc;
+}
+
+// In-process sharding (kb_service_create_multi): one rank's share of a suggestion WITHOUT a collective -- the local
+// winners (FP64 score, global candidate index, value) come back to the host, which holds every rank's answer in one
+// address space and merges them there (tpe_merge_kernel's rule: best score, lowest index).
+int kb_tpe_suggest_range(kb_ctx *ctx, uint64_t seed, int64_t first, int64_t count, int64_t *out_index, double *out_value,
+                         double *out_score) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_suggest_range: no history set");
+    if (first < 0 || count < 0 || first + count >= (1ll << 32)) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest_range: range outside [0, 2^32)");
+    return tpe_suggest_range(ctx, seed, first, count, false, out_index, out_value, out_score);
 }
 
 // ---------------------------------------------------------------------------------------------------------
