@@ -757,11 +757,15 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
             ctx->small_cap = (int64_t)(blocks * npad);
         }
         KbProf pf(ctx, 5, s);
-        tpe_build_small_kernel<<<dim3((unsigned)D, 2), BUILD_THREADS, 0, s>>>(ctx->d_dims, ctx->d_values, ctx->d_loss, n, D, nb, npad,
+        // every phase of the build ends in a barrier; 256 threads make each of them a third as expensive as 1024, and a
+        // few hundred trials give 1024 threads nothing to do anyway
+        const int threads = n <= 384 ? 256 : BUILD_THREADS;
+        tpe_build_small_kernel<<<dim3((unsigned)D, 2), threads, 0, s>>>(ctx->d_dims, ctx->d_values, ctx->d_loss, n, D, nb, npad,
                                                                              ctx->d_small_keys, ctx->d_small_idx, ctx->d_small_pos,
                                                                              ctx->tpe_merge ? 1 : 0);
         KB_LAUNCH_CHECK(ctx);
     } else {
+    KbProf pf(ctx, 5, s);
     split_kernel<<<1, BUILD_THREADS, 0, s>>>(ctx->d_loss, n, npad, ctx->d_sort_keys, ctx->d_sort_idx, ctx->d_pos);
     KB_LAUNCH_CHECK(ctx);
     if (ctx->n_numeric > 0) {
