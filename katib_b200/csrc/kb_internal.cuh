@@ -142,12 +142,14 @@ struct kb_ctx {
     double *d_tabmem = nullptr;      // arena behind the KbDim table pointers
     size_t tabmem_bytes = 0;
     bool history_ready = false;
+    bool tables_dirty = false;       // history uploaded, tables not built yet (kb_tpe_ensure_tables)
     void *h_up = nullptr;            // pinned staging of the history upload (grow-only) and the event behind its copies
     size_t up_bytes = 0;
     cudaEvent_t ev_up = nullptr;
     std::vector<char> h_dims_sent;   // the descriptor table as last uploaded (d_dims is rewritten only when it differs)
     bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
     bool tpe_prune = false;          // KB_OPT_PRUNE_FAR
+    bool lean_attr_set = false;      // dynamic shared-memory limit of the single-kernel suggest raised
     bool quant_attr_set = false;     // dynamic shared-memory limit of the quantised score kernels raised
     float2 *d_stage_sorted = nullptr;  // [n_cont][chunk] stage_cont in bucket order (pruned scoring)
     int32_t *d_perm = nullptr;         // [n_cont][chunk] chunk-local index of the candidate at each sorted position
@@ -243,6 +245,9 @@ int kb_cmaes_free(kb_ctx *ctx);
 int kb_comm_free(kb_ctx *ctx);
 int kb_comm_allgather(kb_ctx *ctx, const void *send, void *recv, size_t bytes, cudaStream_t s);
 int kb_comm_allreduce_sum_f64(kb_ctx *ctx, double *buf, size_t count, cudaStream_t s);
+int kb_tpe_ensure_tables(kb_ctx *ctx);
+bool kb_tpe_lean_fits(const kb_ctx *ctx, int64_t n_cand);
+int kb_tpe_suggest_lean(kb_ctx *ctx, int64_t n_cand, uint64_t seed, double *out_value);
 int kb_tpe_suggest_range(kb_ctx *ctx, uint64_t seed, int64_t first, int64_t count, int64_t *out_index, double *out_value,
                          double *out_score);
 

@@ -744,7 +744,31 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
         }
         if (dims_changed) ctx->h_dims_sent.assign((const char *)canon.data(), (const char *)canon.data() + dims_b);
     }
+    // The tables are built when something first needs them (kb_tpe_ensure_tables): a small history followed by a small
+    // kb_tpe_suggest is answered by ONE kernel that builds what it needs in shared memory (kb_tpe_small.cu) and never
+    // asks for them.  K / Kpad are known on the host (n_side + 1) either way.
     const int nb = [&] { int a = (int)ceil(0.1 * (double)n); return a > 25 ? 25 : a; }();
+    for (int d = 0; d < D; d++) {
+        KbDim &k = ctx->h_dims[(size_t)d];
+        for (int side = 0; side < 2; side++) {
+            k.K[side] = k.kind == KB_CATEGORICAL ? k.n_choices : (side == 0 ? nb : n - nb) + 1;
+            k.Kpad[side] = k.kind == KB_CATEGORICAL ? k.n_choices : pad_to(k.K[side], KB_TABLE_PAD);
+        }
+    }
+    ctx->n_trials = n;
+    ctx->n_below = nb;
+    ctx->tables_dirty = true;
+    ctx->history_ready = true;
+    return KB_OK;
+}
+
+// Build (once per history) the below / above split and every table of every parameter.  Called, under the context's
+// lock and with its device current, by every entry point that reads the tables.
+int kb_tpe_ensure_tables(kb_ctx *ctx) {
+    if (!ctx->tables_dirty) return KB_OK;
+    const int n = (int)ctx->n_trials, D = ctx->D, nb = ctx->n_below;
+    const int npad = next_pow2((int64_t)n + 1);
+    cudaStream_t s = ctx->stream;
     static const bool small_ok = [] { const char *e = getenv("KB_BUILD_SMALL"); return !(e && e[0] == '0'); }();
     if (n <= KB_BUILD_SMALL_MAX && small_ok) {
         const size_t blocks = (size_t)D * 2;
@@ -786,20 +810,11 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
         KB_LAUNCH_CHECK(ctx);
     }
     }
-    // K / Kpad are known on the host (n_side + 1); p_accept and L stay on the device (kb_tpe_get_parzen fetches them),
-    // so the call returns without synchronising: on the context's stream the kernels above are simply ordered before
-    // any scoring launch; a *_device entry point given another stream waits on ev_build (kb_order_after_build)
+    // p_accept and L stay on the device (kb_tpe_get_parzen fetches them), so nothing here synchronises: on the
+    // context's stream the kernels above are simply ordered before any scoring launch; a *_device entry point given
+    // another stream waits on ev_build (kb_order_after_build)
     KB_CUDA(ctx, cudaEventRecord(ctx->ev_build, s));
-    for (int d = 0; d < D; d++) {
-        KbDim &k = ctx->h_dims[(size_t)d];
-        for (int side = 0; side < 2; side++) {
-            k.K[side] = k.kind == KB_CATEGORICAL ? k.n_choices : (side == 0 ? nb : n - nb) + 1;
-            k.Kpad[side] = k.kind == KB_CATEGORICAL ? k.n_choices : pad_to(k.K[side], KB_TABLE_PAD);
-        }
-    }
-    ctx->n_trials = n;
-    ctx->n_below = nb;
-    ctx->history_ready = true;
+    ctx->tables_dirty = false;
     return KB_OK;
 }
 
@@ -826,6 +841,7 @@ extern "C" int kb_tpe_get_parzen(kb_ctx *ctx, int param, int side, int *K, doubl
     if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_get_parzen: no history set");
     if (param < 0 || param >= ctx->D || (side != 0 && side != 1))
         return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_get_parzen: param/side out of range");
+    { int rc = kb_tpe_ensure_tables(ctx); if (rc) return rc; }
     KbDim k = ctx->h_dims[(size_t)param];
     // kb_tpe_set_history returns without waiting; the context's stream is non-blocking, so plain cudaMemcpy does not
     // order behind the build kernels by itself
@@ -858,8 +874,8 @@ extern "C" int kb_tpe_set_option(kb_ctx *ctx, int option, int value) {
         if (ctx->tpe_merge == (value != 0)) return KB_OK;
         ctx->tpe_merge = value != 0;
         if (!ctx->history_ready) return KB_OK;
-        KbDeviceGuard g(ctx->device);  // tables are rebuilt under the new setting from the history on the device
-        return tpe_load_history(ctx, "kb_tpe_set_option", ctx->n_trials, 0, nullptr, nullptr);
+        ctx->tables_dirty = true;  // rebuilt under the new setting, from the history on the device, at the next use
+        return KB_OK;
     }
     if (option == KB_OPT_PRUNE_FAR) {  // both table forms are always built: nothing to redo
         ctx->tpe_prune = value != 0;

@@ -75,6 +75,7 @@ extern "C" int kb_tpe_sample_candidates(kb_ctx *ctx, int64_t n, uint64_t seed, d
     if (n < 0 || n >= (1ll << 32)) return kb_fail(ctx, KB_ERR_UNSUPPORTED, "kb_tpe_sample_candidates: n outside [0, 2^32)");
     if (n > 0 && !cand_host && !cand_device) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_sample_candidates: no output buffer");
     if (n == 0) return KB_OK;
+    { int rc = kb_tpe_ensure_tables(ctx); if (rc) return rc; }
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
     KB_CUDA(ctx, kb_order_after_build(ctx, s));
     double *d_out = cand_device;

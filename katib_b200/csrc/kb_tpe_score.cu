@@ -27,6 +27,7 @@
 
 #include "kb_internal.cuh"
 #include "kb_tpe_sample.cuh"
+#include "kb_tpe_rescore.cuh"
 
 #define KB_EPS 1e-12
 // kb_tpe_suggest with a communicator: candidate counts from here on are sharded over the ranks (one collective); below
@@ -1166,45 +1167,6 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
 
 struct KbCand { double x; unsigned long long idx; double score; };
 
-__device__ double rescore_value(const KbDim &dm, double x, int lane) {
-    double out[2];
-    for (int side = 0; side < 2; side++) {
-        const int K = dm.K[side];
-        const double *mu = dm.mu[side], *sg = dm.sigma[side];
-        if (dm.q > 0.0) {
-            const double *w = dm.w[side];
-            double ub = x + dm.q / 2.0; ub = ub > dm.hi ? dm.hi : ub;
-            double lb = x - dm.q / 2.0; lb = lb < dm.lo ? dm.lo : lb;
-            double p = 0.0;
-            for (int j = lane; j < K; j += 32) {
-                double den = sqrt(2.0) * sg[j];
-                den = den < KB_EPS ? KB_EPS : den;
-                p += w[j] * (0.5 * (1.0 + erf((ub - mu[j]) / den)) - 0.5 * (1.0 + erf((lb - mu[j]) / den)));
-            }
-            for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
-            out[side] = log(p + KB_EPS) - log(dm.p_accept[side] + KB_EPS);
-        } else {
-            const double *logc = dm.logc[side];
-            double m = -INFINITY;
-            for (int j = lane; j < K; j += 32) {
-                double s = sg[j] > KB_EPS ? sg[j] : KB_EPS;
-                double dd = (x - mu[j]) / s;
-                m = fmax(m, -0.5 * (dd * dd) + logc[j]);
-            }
-            for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-            double acc = 0.0;
-            for (int j = lane; j < K; j += 32) {
-                double s = sg[j] > KB_EPS ? sg[j] : KB_EPS;
-                double dd = (x - mu[j]) / s;
-                acc += exp(-0.5 * (dd * dd) + logc[j] - m);
-            }
-            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-            out[side] = log(acc) + m;
-        }
-    }
-    return out[0] - out[1];
-}
-
 // table -> dense list of the entries still within the margin of the FINAL maximum
 __global__ void __launch_bounds__(RS_THREADS)
 tpe_compact_kernel(const KbDim *__restrict__ dims, const int *__restrict__ numeric_dims, const KbSelect *__restrict__ sel,
@@ -1618,7 +1580,7 @@ static int tpe_precheck(kb_ctx *ctx, int64_t n_cand, const void *cand, const cha
     if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "%s: call kb_tpe_set_history first", who);
     if (n_cand < 0 || n_cand >= (1ll << 32)) return kb_fail(ctx, KB_ERR_UNSUPPORTED, "%s: n_cand outside [0, 2^32)", who);
     if (n_cand > 0 && !cand) return kb_fail(ctx, KB_ERR_INVALID, "%s: cand is NULL", who);
-    return KB_OK;
+    return kb_tpe_ensure_tables(ctx);
 }
 
 // candidates on the host: chunked, H2D double-buffered on the copy stream, compute on the ctx stream
@@ -1740,6 +1702,10 @@ extern "C" int kb_tpe_suggest(kb_ctx *ctx, int64_t n_ei_candidates, uint64_t see
     int world = 1, rank = 0;
     kb_comm_world(ctx, &world, &rank);
     const bool sharded = world > 1 && n >= KB_SUGGEST_SHARD_MIN;
+    // a fresh small history and a small request: one kernel builds both estimators in shared memory, draws, scores and
+    // picks (kb_tpe_small.cu); the tables in HBM are not built for it
+    if (ctx->tables_dirty && kb_tpe_lean_fits(ctx, n)) return kb_tpe_suggest_lean(ctx, n, seed, out_value);
+    { int rc = kb_tpe_ensure_tables(ctx); if (rc) return rc; }
     {   // small problems (Katib's own: 24 candidates): the fused single-kernel path
         int64_t kmax = 1;
         for (int d = 0; d < ctx->D; d++) {
@@ -1806,6 +1772,7 @@ int kb_tpe_suggest_range(kb_ctx *ctx, uint64_t seed, int64_t first, int64_t coun
     KbDeviceGuard g(ctx->device);
     if (!ctx->history_ready) return kb_fail(ctx, KB_ERR_STATE, "kb_tpe_suggest_range: no history set");
     if (first < 0 || count < 0 || first + count >= (1ll << 32)) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_suggest_range: range outside [0, 2^32)");
+    { int rc = kb_tpe_ensure_tables(ctx); if (rc) return rc; }
     return tpe_suggest_range(ctx, seed, first, count, false, out_index, out_value, out_score);
 }
 
