@@ -419,40 +419,79 @@ __device__ void parzen_body(KbDim &dm, int d, int side, const double *__restrict
         const int Kg = s_int[nt - 1], Ko = K - Kg;
         int bg = s_int[tid] - c, bo = b0 - bg;
         __syncthreads();
-        // The other components that sit ON the grid too (wider sigma: the whole below side of a dense history) get a
-        // table row of their own: for an on-grid candidate their bin integral depends only on the integer offset as
-        // well, with the component's own sigma.  Rows are handed out in table order while the budget lasts
-        // (KB_LUT2_FLOATS); the entry's .w then carries 0x40000000 | row << 16 | grid index of mu.
+        // The other components that sit ON the grid too (wider sigma: the below side of a dense history, and the two
+        // components at the ends of every run of equal values on the above side, whose neighbour distance is one step)
+        // get a table row as well: for an on-grid candidate their bin integral depends only on the integer offset
+        // too, with their own sigma.  Components with the same sigma share a row, so a handful of rows serves them
+        // all; rows are numbered in order of first appearance while the budget lasts (KB_LUT2_FLOATS).  The entry's .w
+        // then carries 0x40000000 | row << 16 | grid index of mu (bit 29: this entry is the row's first user).
         const int rowlen = 2 * G - 1;
         const int max_rows = G > 0 ? min(KB_LUT2_FLOATS / rowlen, 255) : 0;
+        const int Kl = min(Ko, 2048);  // entries considered (the pairing below is quadratic)
         for (int j = b0; j < b1; j++) {
             const float4 Bj = tab[2 * j + 1];
             const int code = __float_as_int(Bj.w);
             if (code != 0) { keys[bg] = (double)fabsf(Bj.z); idx[bg] = (uint32_t)code; bg++; }
             else {
-                float4 Bo = Bj;
-                if (bo < max_rows) {
+                uint32_t mark = 0u;
+                if (max_rows > 0 && bo < Kl) {
                     const double gi = (mu[j] - (low + 0.5 * dm.q)) / dm.q, gr = rint(gi);
-                    if (fabs(gi - gr) <= 1e-9 && gr >= 0.0 && gr < (double)G) Bo.w = __int_as_float(0x40000000 | (bo << 16) | (int)gr);
+                    if (fabs(gi - gr) <= 1e-9 && gr >= 0.0 && gr < (double)G) mark = 0x80000000u | (uint32_t)gr;
                 }
-                keys[Kg + bo] = sg[j];  // for the row below (keys[] holds K <= npad entries)
-                to[2 * bo] = tab[2 * j]; to[2 * bo + 1] = Bo; bo++;
+                keys[Kg + bo] = sg[j];  // keys[] and idx[] hold K <= npad entries: [0, Kg) look-up class, [Kg, K) the others
+                idx[Kg + bo] = mark;
+                to[2 * bo] = tab[2 * j]; to[2 * bo + 1] = Bj; bo++;
             }
         }
         const float4 Z = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int j = Ko + tid; j < (Ko + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { to[2 * j] = Z; to[2 * j + 1] = Z; }
         __syncthreads();
-        {   // rows of the second table: row o belongs to other-entry o (only entries with the 0x40000000 mark are read)
-            const int nrow = min(Ko, max_rows);
+        for (int o = tid; o < Kl; o += nt) {  // pass 1: is this entry the first on-grid one with its sigma?
+            if (!(idx[Kg + o] & 0x80000000u)) continue;
+            const double so = keys[Kg + o];
+            bool rep = true;
+            for (int e = 0; e < o; e++)
+                if ((idx[Kg + e] & 0x80000000u) && keys[Kg + e] == so) { rep = false; break; }
+            float4 Bo = to[2 * o + 1];
+            Bo.w = __int_as_float(0x40000000 | (rep ? 0x20000000 : 0));
+            to[2 * o + 1] = Bo;
+        }
+        __syncthreads();
+        for (int o = tid; o < Kl; o += nt) {  // pass 2: row = number of first-users before this sigma's first user
+            if (!(idx[Kg + o] & 0x80000000u)) continue;
+            const double so = keys[Kg + o];
+            int f = o;
+            for (int e = 0; e < o; e++)
+                if ((idx[Kg + e] & 0x80000000u) && keys[Kg + e] == so) { f = e; break; }
+            int row = 0;
+            for (int e = 0; e < f; e++) row += (__float_as_int(to[2 * e + 1].w) & 0x20000000) ? 1 : 0;
+            idx[Kg + o] = 0x80000000u | ((uint32_t)min(row, 0x7FFF) << 16) | (idx[Kg + o] & 0xFFFFu);
+        }
+        __syncthreads();
+        {   // pass 3: final marks; the first users are listed by row, then the rows are computed entry by entry in parallel
             float *lut2 = dm.lut2[side];
-            for (int e = tid; e < nrow * rowlen; e += nt) {
-                const int o = e / rowlen, k = e - o * rowlen;
-                double den = sqrt(2.0) * keys[Kg + o];
+            if (tid == 0) s_int[BUILD_THREADS - 1] = 0;  // number of rows (rows < 256 never reach this slot)
+            __syncthreads();
+            for (int o = tid; o < Kl; o += nt) {
+                if (!(idx[Kg + o] & 0x80000000u)) continue;
+                const int row = (int)((idx[Kg + o] >> 16) & 0x7FFFu), gmu = (int)(idx[Kg + o] & 0xFFFFu);
+                float4 Bo = to[2 * o + 1];
+                const bool rep = (__float_as_int(Bo.w) & 0x20000000) != 0;
+                Bo.w = row < max_rows ? __int_as_float(0x40000000 | (rep ? 0x20000000 : 0) | (row << 16) | gmu) : 0.f;
+                to[2 * o + 1] = Bo;
+                if (rep && row < max_rows) { s_int[row] = o; atomicMax(&s_int[BUILD_THREADS - 1], row + 1); }
+            }
+            __syncthreads();
+            const int n_rows = s_int[BUILD_THREADS - 1];
+            for (int e = tid; e < n_rows * rowlen; e += nt) {
+                const int row = e / rowlen, k = e - row * rowlen;
+                double den = sqrt(2.0) * keys[Kg + s_int[row]];
                 if (den < KB_EPS) den = KB_EPS;
                 const double rr = 1.0 / den, h = 0.5 * dm.q * rr;
                 const double y = fabs((double)(k - (G - 1))) * dm.q * rr;
                 lut2[e] = (float)(erfc(y - h) - erfc(y + h));
             }
+            __syncthreads();
         }
         const int seg2 = (Kg + nt - 1) / nt, g0 = min(Kg, tid * seg2), g1 = min(Kg, g0 + seg2);
         int h = 0;

@@ -199,13 +199,19 @@ tpe_suggest_lean_kernel(const KbDim *__restrict__ dims, const double *__restrict
         // sampleCategorical tables: weighted bincount in trial order + prior weight, normalised; score = log pl - log pg
         const int C = g.n_choices;
         double *p0 = a_mu, *p1 = a_sg, *sc = a_w;
+        // every trial's ramp weight once, in parallel (the divisions inside ln_ramp are what a serial loop cannot afford);
+        // the per-category sums below then run over the trials IN ORDER, the oracle's rounding
+        for (int i = tid; i < n; i += LN_THREADS) {
+            s_loss[i] = ln_ramp(s_pos[i], s_flag[i] == 0 ? nb : n - nb);
+            itmp[i] = (int)s_val[i];
+        }
+        __syncthreads();
         for (int side = 0; side < 2; side++) {
-            const int m = side == 0 ? nb : n - nb;
             double *p = side == 0 ? p0 : p1;
             for (int c = tid; c < C; c += LN_THREADS) {
                 double acc = 0.0;
                 for (int i = 0; i < n; i++)
-                    if (s_flag[i] == side && (int)s_val[i] == c) acc += ln_ramp(s_pos[i], m);
+                    if (s_flag[i] == side && itmp[i] == c) acc += s_loss[i];
                 p[c] = acc + 1.0;  // prior_weight
             }
             __syncthreads();
@@ -325,10 +331,11 @@ int kb_tpe_suggest_lean(kb_ctx *ctx, int64_t n_cand, uint64_t seed, double *out_
     {
         KbProf pf(ctx, 3, s);
         tpe_suggest_lean_kernel<<<(unsigned)D, LN_THREADS, bytes, s>>>(ctx->d_dims, ctx->d_values, ctx->d_loss, n, D, ctx->n_below,
-                                                                       ctx->tpe_merge ? 1 : 0, (int)n_cand, seed, plan, ctx->d_win);
+                                                                       ctx->tpe_merge ? 1 : 0, (int)n_cand, seed, plan, ctx->h_win);
         KB_LAUNCH_CHECK(ctx);
     }
-    KB_CUDA(ctx, cudaMemcpyAsync(ctx->h_win, ctx->d_win, sizeof(KbWinner) * (size_t)D, cudaMemcpyDeviceToHost, s));
+    // the D winners (24 B each) are written by the kernel straight into the pinned host mirror (mapped into the device's
+    // address space under unified addressing): no copy to enqueue, the stream synchronisation is the only wait
     KB_CUDA(ctx, cudaStreamSynchronize(s));
     for (int d = 0; d < D; d++) out_value[d] = ctx->h_win[d].value;
     return KB_OK;
