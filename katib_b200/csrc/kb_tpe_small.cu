@@ -20,7 +20,8 @@
 #include "kb_tpe_sample.cuh"
 #include "kb_tpe_rescore.cuh"
 
-#define LN_THREADS 256
+#define LN_MAXT 1024          // most threads per CTA (KB_LEAN_THREADS picks 256 / 512 / 1024 for measurements)
+#define LN_THREADS ((int)blockDim.x)
 #define LN_MAX_N 512          // trials
 #define LN_MAX_K (LN_MAX_N + 1)
 #define LN_MAX_CAND 256       // EI candidates
@@ -44,7 +45,7 @@ __device__ __forceinline__ int ln_block_sum(int v, int *s_red) {
     if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
     __syncthreads();
     int t = 0;
-    for (int w = 0; w < LN_THREADS / 32; w++) t += s_red[w];
+    for (int w = 0; w < (int)blockDim.x / 32; w++) t += s_red[w];
     return t;
 }
 
@@ -156,12 +157,12 @@ __device__ int ln_parzen(const double *obs_val, const int *obs_pos, int m, doubl
 // shared-memory plan of one CTA (doubles first, then ints); LA = max(n + 1, n_choices of the widest categorical)
 struct LnPlan {
     int n, km, la, nc;
-    __host__ __device__ size_t doubles() const { return (size_t)2 * n + (2 * km + 1) + 4 * (size_t)la + 4 * 32 + 2 * (size_t)nc + LN_THREADS; }
-    __host__ __device__ size_t ints() const { return (size_t)3 * n + km + 2 * LN_THREADS; }
+    __host__ __device__ size_t doubles() const { return (size_t)2 * n + (2 * km + 1) + 4 * (size_t)la + 4 * 32 + 2 * (size_t)nc + LN_MAXT; }
+    __host__ __device__ size_t ints() const { return (size_t)3 * n + km + 2 * LN_MAXT; }
     __host__ __device__ size_t bytes() const { return doubles() * sizeof(double) + ints() * sizeof(int); }
 };
 
-__global__ void __launch_bounds__(LN_THREADS)
+__global__ void __launch_bounds__(LN_MAXT)
 tpe_suggest_lean_kernel(const KbDim *__restrict__ dims, const double *__restrict__ values, const double *__restrict__ loss_g, int n,
                         int D, int nb, int merge, int n_cand, uint64_t seed, LnPlan plan, KbWinner *__restrict__ win) {
     extern __shared__ __align__(16) double ln_smem[];
@@ -171,8 +172,8 @@ tpe_suggest_lean_kernel(const KbDim *__restrict__ dims, const double *__restrict
     double *a_mu = tmp + (2 * plan.km + 1), *a_sg = a_mu + plan.la, *a_w = a_sg + plan.la, *a_lc = a_w + plan.la;
     double *b_mu = a_lc + plan.la, *b_sg = b_mu + 32, *b_w = b_sg + 32, *b_lc = b_w + 32;
     double *s_x = b_lc + 32, *s_sc = s_x + plan.nc, *s_bs = s_sc + plan.nc;
-    int *s_flag = reinterpret_cast<int *>(s_bs + LN_THREADS), *s_pos = s_flag + plan.n, *s_opos = s_pos + plan.n;
-    int *itmp = s_opos + plan.n, *s_red = itmp + plan.km, *s_bi = s_red + LN_THREADS;
+    int *s_flag = reinterpret_cast<int *>(s_bs + LN_MAXT), *s_pos = s_flag + plan.n, *s_opos = s_pos + plan.n;
+    int *itmp = s_opos + plan.n, *s_red = itmp + plan.km, *s_bi = s_red + LN_MAXT;
     if (tid == 0) s_dm = dims[d];
     for (int i = tid; i < n; i += LN_THREADS) s_loss[i] = loss_g[i];
     __syncthreads();
@@ -330,7 +331,8 @@ int kb_tpe_suggest_lean(kb_ctx *ctx, int64_t n_cand, uint64_t seed, double *out_
     }
     {
         KbProf pf(ctx, 3, s);
-        tpe_suggest_lean_kernel<<<(unsigned)D, LN_THREADS, bytes, s>>>(ctx->d_dims, ctx->d_values, ctx->d_loss, n, D, ctx->n_below,
+        static const int threads = [] { const char *e = getenv("KB_LEAN_THREADS"); const int t = e ? atoi(e) : 0; return t == 256 || t == 512 || t == 1024 ? t : 512; }();
+        tpe_suggest_lean_kernel<<<(unsigned)D, threads, bytes, s>>>(ctx->d_dims, ctx->d_values, ctx->d_loss, n, D, ctx->n_below,
                                                                        ctx->tpe_merge ? 1 : 0, (int)n_cand, seed, plan, ctx->h_win);
         KB_LAUNCH_CHECK(ctx);
     }
