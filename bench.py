@@ -471,7 +471,8 @@ def main():
     launch_rows = min(n_local, 1 << int(os.environ.get("KB_CHUNK_LOG2", "22")))  # candidates per kernel launch (staged chunk)
     ce_cont = float(n_local) * n_cont * (K_l + K_g) * args.steps
     ce_quant = float(n_local) * n_quant * (K_l + K_g) * args.steps
-    names = ["tpe_stage_kernel", "tpe_score_cont_kernel", "tpe_score_quant_kernel", "tpe_rescore+pick"]
+    names = ["tpe_stage_kernel", "tpe_score_cont_kernel", "tpe_score_quant_grid_kernel (+ tpe_score_quant_kernel for off-grid tiles: none here)",
+             "tpe_rescore+pick"]
     tot = sum(p[0] for p in prof.values()) or 1.0
     kern = []
     for k in range(4):
@@ -480,20 +481,22 @@ def main():
         if k == 1 and ms_k > 0:
             a = ce_cont / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
-                       frac=a / peaks["mufu_ex2_gops"], traffic=182.6e6 * launch_rows / float(1 << 20),
-                       traffic_note=f"dram read+write bytes per launch: 182.6 MB measured by ncu --set full on a 2^20-candidate launch "
-                                    f"(profiles/r01_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches "
+                       frac=a / peaks["mufu_ex2_gops"], traffic=182.2e6 * launch_rows / float(1 << 20),
+                       note="1 of every 16 exponentials is computed on the FMA pipe (packed FP32 polynomial), so the kernel can "
+                            "read slightly above 15/16 of what MUFU alone allows; every (candidate, component) pair is evaluated",
+                       traffic_note=f"dram read+write bytes per launch: 182.2 MB measured by ncu --set full on a 2^20-candidate launch "
+                                    f"(profiles/r02_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches "
                                     "(the traffic is the candidate columns, read once)")
         if k == 2 and ms_k > 0:
             a = ce_quant / (ms_k * 1e-3) / 1e9
             ent.update(bound="fp32", unit="G bin-integral evals/s (1 FP32 FMA lane-op each as executed: look-up class)", achieved=a,
-                       peak=peaks["fp32_gfma"], frac=a / peaks["fp32_gfma"], traffic=195.6e6 * launch_rows / float(1 << 20),
+                       peak=peaks["fp32_gfma"], frac=a / peaks["fp32_gfma"], traffic=200.3e6 * launch_rows / float(1 << 20),
                        note="every (candidate, component) pair of this workload is an on-grid pair: its bin integral is a table "
                             "value times the component weight, one FP32 FMA lane-op; the bound is the FP32 FMA pipe "
                             "(kb_peak_measure FFMA micro-kernel).  Against the erf formulation's SFU roofline (2 exp per "
                             f"evaluation) the same rate is {a / (peaks['mufu_ex2_gops'] / 2):.2f}x",
-                       traffic_note=f"dram read+write bytes per launch: 195.6 MB measured by ncu --set full on a 2^20-candidate launch, "
-                                    f"scaled to this run's {launch_rows}-candidate launches")
+                       traffic_note=f"dram read+write bytes per launch: 200.3 MB measured by ncu --set full on a 2^20-candidate launch "
+                                    f"(profiles/r02_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches")
         if k == 0 and ms_k > 0:
             bytes_alg = float(n_local) * D * 8 * args.steps + float(n_local) * (n_cont * 8 + n_quant * 16) * args.steps
             a = bytes_alg / (ms_k * 1e-3) / 1e9
