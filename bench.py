@@ -32,6 +32,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 N_HISTORY = 10_000
+JSON_OUT = sys.stdout  # main() replaces it by a duplicate of the original stdout before anything native can print
 # admission margins of the near-tie table (kb_tpe_score.cu: KB_MARGIN_CONT / KB_MARGIN_QUANT)
 MARGIN_CONT, MARGIN_QUANT = 4e-6, 1.5e-5
 CAT_CHOICES = [2, 3, 4, 6, 8, 12, 16]
@@ -208,11 +209,15 @@ def main():
         if int(os.environ.get("RANK", "0")) == 0:
             bench_workloads.WORKLOADS[args.workload](args)
         return
-    # NCCL reports its communicators (rank count, transport) at level INFO; that log goes to stderr so that stdout keeps
-    # its one JSON line (NCCL's default sink is stdout)
+    # NCCL reports its communicators (rank count, transport) at level INFO on the process's stdout (fd 1).  stdout must
+    # carry exactly one JSON line, so fd 1 is pointed at stderr for everything native and the JSON line goes to a
+    # duplicate of the original stdout (JSON_OUT)
+    global JSON_OUT
+    sys.stdout.flush()
+    JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     os.environ.setdefault("NCCL_DEBUG", os.environ.get("KB_NCCL_DEBUG", "INFO"))
     os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -249,7 +254,8 @@ def main():
                              "sample": f"{n_sample} candidates x {D} params x {N_HISTORY}-trial history per step "
                                        "(goptuna is Go and un-vendored: the oracle port stands in; it scores one "
                                        "candidate block per host thread)"},
-            "e2e": {"value": v, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+            "e2e": {"value": v, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}),
+            file=JSON_OUT, flush=True)
         return
 
     # ------------------------------------------------------------------ our arm
@@ -534,7 +540,7 @@ def main():
            "suggest_whole_set": suggest, "merged_duplicates": merged, "pruned": pruned, "latency": latency,
            "winners_vs_oracle": winners_vs_oracle, "score_error_max": score_error, "secondary": secondary,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
-    print(json.dumps(out), flush=True)
+    print(json.dumps(out), file=JSON_OUT, flush=True)
     shutdown()
 
 
