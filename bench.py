@@ -216,7 +216,7 @@ def main():
     sys.stdout.flush()
     JSON_OUT = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
-    os.environ.setdefault("NCCL_DEBUG", os.environ.get("KB_NCCL_DEBUG", "INFO"))
+    os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "INFO")  # the box presets a quieter level
     os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
