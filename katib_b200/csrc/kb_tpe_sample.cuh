@@ -48,13 +48,14 @@ __device__ __forceinline__ double tpe_sample_one(const KbDim &dm, const Philox &
     const double *w = dm.w[0], *mu = dm.mu[0], *sg = dm.sigma[0];
     double x = 0.5 * (dm.lo + dm.hi);
     for (uint32_t attempt = 0; attempt < SAMPLE_MAX_TRIES; attempt++) {
+        // one Philox block per attempt: 32 bits pick the component, 53 bits the radius, 32 bits the angle
         const uint4 r = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d, attempt + 1u);
-        const uint4 r2 = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d | 0x80000000u, attempt + 1u);
-        const double u = u01(r.x, r.y);
+        const double u = ((double)r.x + 0.5) * (1.0 / 4294967296.0);
         double acc = 0.0;
         int a = K - 1;
         for (int j = 0; j < K; j++) { acc += w[j]; if (u < acc) { a = j; break; } }
-        double u1 = u01(r.z, r.w), u2 = u01(r2.x, r2.y);
+        double u1 = u01(r.y, r.z);
+        const double u2 = ((double)r.w + 0.5) * (1.0 / 4294967296.0);
         u1 = u1 < 1e-300 ? 1e-300 : u1;
         const double z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);  // Box-Muller
         const double draw = mu[a] + sg[a] * z;

@@ -1402,9 +1402,11 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
         KB_CUDA(ctx, cudaMemcpy(sc->d_slot_of_dim, slot_of.data(), sizeof(int) * (size_t)D, cudaMemcpyHostToDevice));
         KB_CUDA(ctx, cudaMemcpy(sc->d_numeric_dims, numeric.data(), sizeof(int) * slots, cudaMemcpyHostToDevice));
     }
-    {   // near-tie table: one slot per 32 candidates, within [2^12, 2^20] per numeric parameter
+    {   // near-tie table: one slot per 256 candidates, within [2^12, 2^20] per numeric parameter (it holds the distinct
+        // values seen within the margin of the running maximum -- hundreds at the headline size; a flat landscape
+        // overflows it and the pass is repeated with a table 16 times larger, tpe_retry_overflow)
         unsigned int want = KB_TIE_SLOTS_MIN;
-        while (want < KB_TIE_SLOTS_MAX && (int64_t)want * 32 < n_cand) want <<= 1;
+        while (want < KB_TIE_SLOTS_MAX && (int64_t)want * 256 < n_cand) want <<= 1;
         if (want < ctx->tie_slots_floor) want = ctx->tie_slots_floor;  // raised after an overflow (tpe_retry_overflow)
         if (want > ctx->tie_slots) {
             const size_t nn = (size_t)(ctx->n_numeric > 0 ? ctx->n_numeric : 1);
