@@ -796,6 +796,14 @@ int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *
     return KB_OK;
 }
 
+// canonical order and signs for eigenvectors given as rows of Vt with eigenvalues lam (both device): w ascending,
+// V[i*n+j] = component i of eigenvector j, largest-magnitude component positive
+int kb_eigh_canonical(kb_ctx *ctx, int n, const double *Vt, const double *lam, double *w, double *V, cudaStream_t st) {
+    eigh_order_kernel<<<(unsigned)n, 128, 0, st>>>(n, Vt, lam, w, V);
+    KB_LAUNCH_CHECK(ctx);
+    return KB_OK;
+}
+
 extern "C" int kb_eigh(kb_ctx *ctx, int n, const double *A, double *w, double *V) {
     if (!ctx) return KB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);

@@ -13,6 +13,8 @@ size_t kb_eigh_workspace_bytes(int n);
 int kb_eigh_device(kb_ctx *ctx, int n, const double *d_A, double shift, double *d_w, double *d_V, void *workspace,
                    cudaStream_t st, const double *d_V0t, int *sweeps_out);
 
+int kb_eigh_canonical(kb_ctx *ctx, int n, const double *Vt, const double *lam, double *w, double *V, cudaStream_t st);
+
 struct EighShared {   // device scalars of one eigensolve
     int rotated;      // rotations applied in the current sweep
     int sweeps;
