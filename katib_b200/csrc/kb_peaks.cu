@@ -73,6 +73,40 @@ __global__ void __launch_bounds__(PK_THREADS) peak_write_kernel(double2 *out, si
 __global__ void __launch_bounds__(PK_THREADS) peak_copy_kernel(const double2 *__restrict__ in, double2 *__restrict__ out, size_t n2) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t)gridDim.x * blockDim.x) __stcs(out + i, __ldcs(in + i));
 }
+// FFMA2 and scalar FFMA interleaved (8 packed + 8 scalar chains): do the two forms share one pipe or run side by side?
+__global__ void __launch_bounds__(PK_THREADS) peak_ffma_mix_kernel(float *out, float seed) {
+    float2 a[8];
+    float b[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { a[i] = make_float2(seed + (float)(threadIdx.x + i), seed - (float)i); b[i] = seed * (float)(i + 1); }
+    const float2 m = make_float2(1.000001f, 0.999999f), c = make_float2(seed, seed);
+    for (int it = 0; it < PK_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) { a[i] = __ffma2_rn(a[i], m, c); b[i] = fmaf(b[i], m.x, c.x); }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += a[i].x + a[i].y + b[i];
+    if (s == 123.456f) out[0] = s;
+}
+// FFMA2 with two varying 64-bit register operands (accumulator and multiplicand), the grid kernel's operand pattern
+__global__ void __launch_bounds__(PK_THREADS) peak_ffma2_2op_kernel(float *out, float seed) {
+    float2 a[8], t[4];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = make_float2(seed + (float)(threadIdx.x + i), seed - (float)i);
+#pragma unroll
+    for (int i = 0; i < 4; i++) t[i] = make_float2(1.0f + 1e-7f * (float)(threadIdx.x + i), 1.0f - 1e-7f * (float)i);
+    float w = seed * 1e-9f;
+    for (int it = 0; it < PK_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] = __ffma2_rn(make_float2(w, w), t[i & 3], a[i]);
+        w += 1e-12f;
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += a[i].x + a[i].y;
+    if (s == 123.456f) out[0] = s;
+}
 
 extern "C" int kb_peak_measure(kb_ctx *ctx, int which, double *out) {
     if (!ctx || !out) return KB_ERR_INVALID;
@@ -98,6 +132,8 @@ extern "C" int kb_peak_measure(kb_ctx *ctx, int which, double *out) {
             case 2: peak_dfma_kernel<<<grid, PK_THREADS, 0, s>>>((double *)buf, 0.5); work = (double)grid * PK_THREADS * PK_ITERS * 8; break;
             case 3: peak_write_kernel<<<sms * 16, PK_THREADS, 0, s>>>((double2 *)buf, bytes / 16); work = (double)bytes; break;
             case 5: peak_ffma2_kernel<<<grid, PK_THREADS, 0, s>>>((float *)buf, 0.5f); work = (double)grid * PK_THREADS * PK_ITERS * 16; break;
+            case 6: peak_ffma_mix_kernel<<<grid, PK_THREADS, 0, s>>>((float *)buf, 0.5f); work = (double)grid * PK_THREADS * PK_ITERS * 24; break;
+            case 7: peak_ffma2_2op_kernel<<<grid, PK_THREADS, 0, s>>>((float *)buf, 0.5f); work = (double)grid * PK_THREADS * PK_ITERS * 16; break;
             case 4: peak_copy_kernel<<<sms * 16, PK_THREADS, 0, s>>>((const double2 *)buf, (double2 *)((char *)buf + bytes), bytes / 16); work = 2.0 * (double)bytes; break;
             default: cudaFree(buf); return kb_fail(ctx, KB_ERR_INVALID, "kb_peak_measure: which=%d", which);
         }

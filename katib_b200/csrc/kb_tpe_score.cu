@@ -321,9 +321,6 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
 #ifndef SC_SW_DEFAULT
 #define SC_SW_DEFAULT 1
 #endif
-#ifndef KB_CONT_WS_DEFAULT
-#define KB_CONT_WS_DEFAULT 0   // candidates per lane of the FMA warps of the warp-specialised kernel (0: classic kernel)
-#endif
 template <unsigned SC_SW_MASK>
 __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const float2 (&xh)[SC_R / 2],
                                            const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
@@ -457,176 +454,6 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
     }
     if (sel) select_publish<SC_R, SC_THREADS>(sc, tile_base, n, idx_base, d, D, dm, sel, tie, tie_score, slots,
                                                   KB_MARGIN_CONT, cand_raw);
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// Warp-specialised form of the continuous kernel.  In tpe_score_cont_kernel every warp alternates between FMA-pipe
-// work and MUFU.EX2; once the MIO queue in front of the XU pipe is full a warp stalls there, in order, with its FMA
-// instructions behind it -- which is why moving more than 1/16 of the exponentials onto the FMA pipe inside the same
-// instruction stream stopped paying.  Here the two kinds of work live in different warps of one CTA: eight "MUFU warps"
-// run the loop above on 8 candidates per lane, four "FMA warps" (one per SM sub-partition) score RF more candidates
-// per lane with the polynomial exponential only and never wait on the XU pipe, so they soak up the FMA issue slots
-// the MUFU warps leave idle.  All twelve warps share the table stages and their barriers.  Tile = 2048 + 128 RF.
-// ---------------------------------------------------------------------------------------------------------
-#define WS_MUFU_THREADS 256
-#define WS_FMA_THREADS 128
-#define WS_THREADS (WS_MUFU_THREADS + WS_FMA_THREADS)
-
-// 32 components, RF candidates (RF / 2 pairs), every 2^e by kb_ex2_fma2; two components in lockstep
-template <int RF>
-__device__ __forceinline__ void cont_group_fma(const float4 *__restrict__ tab, const float2 (&xh)[SC_R / 2],
-                                               const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
-#pragma unroll 4
-    for (int jj = 0; jj < SC_GROUP; jj += 2) {
-        const float4 A0 = tab[2 * jj], B0 = tab[2 * jj + 1], A1 = tab[2 * jj + 2], B1 = tab[2 * jj + 3];
-        float2 e0[RF / 2], e1[RF / 2];
-#pragma unroll
-        for (int p = 0; p < RF / 2; p++) {
-            float2 u = __fadd2_rn(__fadd2_rn(xh[p], make_float2(A0.x, A0.y)), xl[p]);
-            float2 t = __ffma2_rn(u, make_float2(A0.z, A0.w), make_float2(B0.x, B0.y));
-            e0[p] = __ffma2_rn(make_float2(-t.x, -t.y), t, make_float2(B0.z, B0.w));
-            u = __fadd2_rn(__fadd2_rn(xh[p], make_float2(A1.x, A1.y)), xl[p]);
-            t = __ffma2_rn(u, make_float2(A1.z, A1.w), make_float2(B1.x, B1.y));
-            e1[p] = __ffma2_rn(make_float2(-t.x, -t.y), t, make_float2(B1.z, B1.w));
-        }
-#pragma unroll
-        for (int p = 0; p < RF / 2; p++) {
-            const float2 v0 = kb_ex2_fma2(e0[p]), v1 = kb_ex2_fma2(e1[p]);
-            a32[p] = __fadd2_rn(a32[p], __fadd2_rn(v0, v1));
-        }
-    }
-}
-
-// select_publish for per-thread candidate lists: ci[r] = chunk-local candidate index of slot r, or -1
-template <int R, int THREADS>
-__device__ __forceinline__ void select_publish_list(const float (&sc)[R], const int (&ci)[R], long long idx_base, int d, int D,
-                                                    const KbDim &dm, KbSelect *sel, KbTie *tie, float *tie_score,
-                                                    unsigned int slots, float margin, KbRaw cand_raw) {
-    __shared__ float s_wmax[THREADS / 32];
-    __shared__ float s_thr;
-    float best = -INFINITY;
-#pragma unroll
-    for (int r = 0; r < R; r++)
-        if (ci[r] >= 0) best = fmaxf(best, sc[r]);
-    for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
-    if ((threadIdx.x & 31) == 0) s_wmax[threadIdx.x >> 5] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float b = s_wmax[0];
-        for (int w = 1; w < THREADS / 32; w++) b = fmaxf(b, s_wmax[w]);
-        const unsigned int mine = kb_f32_orderable(b);
-        const unsigned int old = atomicMax(&sel[d].gmax_bits, mine);
-        const float g = kb_f32_from_orderable(old > mine ? old : mine);
-        const float thr = g - margin * fmaxf(1.0f, fabsf(g));
-        s_thr = b >= thr ? thr : INFINITY;
-    }
-    __syncthreads();
-    const float thr = s_thr;
-    if (thr == INFINITY) return;
-    KbTie *tab = tie + (size_t)dm.numeric_slot * slots;
-    float *tsc = tie_score + (size_t)dm.numeric_slot * slots;
-#pragma unroll
-    for (int r = 0; r < R; r++) {
-        if (ci[r] >= 0 && sc[r] >= thr) {
-            const unsigned long long key = (unsigned long long)__double_as_longlong(kb_raw_value(cand_raw, dm, ci[r], idx_base + ci[r], D, d));
-            tie_insert(tab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + ci[r]), sc[r]);
-        }
-    }
-}
-
-template <int RF, unsigned SW_MASK>
-__global__ void __launch_bounds__(WS_THREADS, 2)
-tpe_score_cont_ws_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
-                         const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
-                         KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
-                         KbRaw cand_raw, double *__restrict__ scores_out) {
-    constexpr int TILE = WS_MUFU_THREADS * SC_R + WS_FMA_THREADS * RF;
-    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
-    __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
-    const int slot = blockIdx.y;
-    const int d = cont_dims[slot];
-    const KbDim &dm = dims[d];
-    const int tile_base = blockIdx.x * TILE;
-    const bool fma_role = threadIdx.x >= WS_MUFU_THREADS;
-    const int nchunk0 = (dm.Kpad[0] + SC_CHUNK - 1) / SC_CHUNK, nchunk1 = (dm.Kpad[1] + SC_CHUNK - 1) / SC_CHUNK;
-    const int nchunks = nchunk0 + nchunk1;
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < SC_STAGES; s++) mbar_init(&s_bar[s], 1);
-        mbar_fence_init();
-    }
-    __syncthreads();
-    if (threadIdx.x == 0)
-        for (int c = 0; c < SC_STAGES && c < nchunks; c++) table_stream_issue(dm, c, nchunk0, s_tab[c], &s_bar[c]);
-
-    int ci[SC_R];  // chunk-local candidate index of every slot of this thread (-1: none)
-    float2 xh[SC_R / 2], xl[SC_R / 2];
-#pragma unroll
-    for (int r = 0; r < SC_R; r++) {
-        int i = fma_role ? (r < RF ? tile_base + WS_MUFU_THREADS * SC_R + r * WS_FMA_THREADS + ((int)threadIdx.x - WS_MUFU_THREADS) : n)
-                         : tile_base + r * WS_MUFU_THREADS + (int)threadIdx.x;
-        ci[r] = i < n ? i : -1;
-        const float2 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float2(0.5f, 0.f);
-        if (r & 1) { xh[r / 2].y = v.x; xl[r / 2].y = v.y; } else { xh[r / 2].x = v.x; xl[r / 2].x = v.y; }
-    }
-    float Shi[SC_R], Slo[SC_R];
-    double logS0[SC_R];
-#pragma unroll
-    for (int r = 0; r < SC_R; r++) { Shi[r] = 0.f; Slo[r] = 0.f; logS0[r] = 0.0; }
-
-    for (int c = 0; c < nchunks; c++) {
-        const int st = c % SC_STAGES;
-        const int side = c < nchunk0 ? 0 : 1;
-        const int cc = side == 0 ? c : c - nchunk0;
-        const int cnt = min(SC_CHUNK, dm.Kpad[side] - cc * SC_CHUNK);
-        mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
-        const float4 *tab = s_tab[st];
-        if (fma_role) {
-            for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
-                float2 a32[SC_R / 2];
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-                cont_group_fma<RF>(tab + 2 * j0, xh, xl, a32);
-#pragma unroll
-                for (int p = 0; p < RF / 2; p++) {
-                    two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
-                    two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
-                }
-            }
-        } else {
-            for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
-                float2 a32[SC_R / 2];
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-                cont_group<SW_MASK>(tab + 2 * j0, xh, xl, a32);
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
-                    two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
-                }
-            }
-        }
-        __syncthreads();  // every thread is done with stage st
-        if (threadIdx.x == 0 && c + SC_STAGES < nchunks)
-            table_stream_issue(dm, c + SC_STAGES, nchunk0, s_tab[st], &s_bar[st]);
-        if (c == nchunk0 - 1) {
-#pragma unroll
-            for (int r = 0; r < SC_R; r++) {
-                if (ci[r] >= 0) logS0[r] = log((double)Shi[r] + (double)Slo[r]) + dm.L[0];
-                Shi[r] = 0.f; Slo[r] = 0.f;
-            }
-        }
-    }
-    float sc[SC_R];
-#pragma unroll
-    for (int r = 0; r < SC_R; r++) {
-        sc[r] = -INFINITY;
-        if (ci[r] >= 0) {
-            const double s64 = logS0[r] - (log((double)Shi[r] + (double)Slo[r]) + dm.L[1]);
-            sc[r] = (float)s64;
-            if (scores_out) scores_out[(size_t)ci[r] * D + d] = s64;
-        }
-    }
-    if (sel) select_publish_list<SC_R, WS_THREADS>(sc, ci, idx_base, d, D, dm, sel, tie, tie_score, slots, KB_MARGIN_CONT, cand_raw);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1656,18 +1483,6 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
         KbProf pf(ctx, 1, s);
         static const int sw = [] { const char *e = getenv("KB_CONT_SW"); return e ? atoi(e) : SC_SW_DEFAULT; }();
-        static const int ws = [] { const char *e = getenv("KB_CONT_WS"); return e ? atoi(e) : KB_CONT_WS_DEFAULT; }();
-        if (ws == 2 || ws == 4) {  // warp-specialised form: tile = 2048 + 128 RF candidates
-            const int tile = WS_MUFU_THREADS * SC_R + WS_FMA_THREADS * ws;
-            dim3 wgrid((unsigned)((n + tile - 1) / tile), (unsigned)ctx->n_cont);
-#define KB_WS_LAUNCH(RF, MASK)                                                                                                   \
-            tpe_score_cont_ws_kernel<RF, MASK><<<wgrid, WS_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont,     \
-                                                                            ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,   \
-                                                                            sc->d_tie_score, ctx->tie_slots, d_cand, d_scores)
-            if (ws == 2) { if (sw == 0) KB_WS_LAUNCH(2, SC_SW_MASK_0); else KB_WS_LAUNCH(2, SC_SW_MASK_1); }
-            else { if (sw == 0) KB_WS_LAUNCH(4, SC_SW_MASK_0); else KB_WS_LAUNCH(4, SC_SW_MASK_1); }
-#undef KB_WS_LAUNCH
-        } else
 #define KB_CONT_LAUNCH(MASK)                                                                                              \
         tpe_score_cont_kernel<MASK><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont,           \
                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,           \
