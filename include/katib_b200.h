@@ -259,7 +259,9 @@ int kb_service_set_option(kb_service *svc, int option, int value);
 
 /* ---- measurement helpers (used by bench.py and the profiles) ----------------------------------
  * which: 0 = MUFU.EX2 Gop/s, 1 = FP32 FFMA GFMA/s, 2 = FP64 DFMA GFMA/s, 3 = HBM write GB/s,
- * 4 = HBM copy GB/s, 5 = FP32 GFMA/s through packed FFMA2.  Runs a saturating micro-kernel on the ctx's device and returns the rate. */
+ * 4 = HBM copy GB/s, 5 = FP32 GFMA/s through packed FFMA2, 6 = FFMA2 and FFMA interleaved (one pipe or two?),
+ * 7 = FFMA2 whose accumulator and multiplicand both change every instruction (the operand pattern of the quantised
+ * grid kernel).  Runs a saturating micro-kernel on the ctx's device and returns the rate. */
 int kb_peak_measure(kb_ctx *ctx, int which, double *out);
 /* Per-kernel-class device timing with CUDA events on the launching stream.  kb_profile(ctx, 1) starts
  * (and clears) the counters, kb_profile(ctx, 0) stops; kb_profile_read returns the summed duration and
