@@ -308,7 +308,8 @@ def main():
     step_dev = lambda: ctx.tpe_score_select_device(n_local, cand.data_ptr(), offset)
     peaks = {}
     if rank == 0:
-        peaks = {"mufu_ex2_gops": ctx.peak(0), "fp32_gfma": ctx.peak(1), "fp64_gfma": ctx.peak(2), "hbm_write_gbs": ctx.peak(3)}
+        peaks = {"mufu_ex2_gops": ctx.peak(0), "fp32_gfma": ctx.peak(1), "fp64_gfma": ctx.peak(2), "hbm_write_gbs": ctx.peak(3),
+                 "fp32_gfma_ffma2_two_varying_operands": ctx.peak(7)}
     for _ in range(args.warmup):
         step_dev()
     launches0 = ctx.launch_count()
@@ -510,7 +511,9 @@ def main():
                        note="every (candidate, component) pair of this workload is an on-grid pair: its bin integral is a table "
                             "value times the component weight, one FP32 FMA lane-op; the bound is the FP32 FMA pipe "
                             "(kb_peak_measure FFMA micro-kernel).  Against the erf formulation's SFU roofline (2 exp per "
-                            f"evaluation) the same rate is {a / (peaks['mufu_ex2_gops'] / 2):.2f}x",
+                            f"evaluation) the same rate is {a / (peaks['mufu_ex2_gops'] / 2):.2f}x; against an FFMA2 stream with this "
+                            "kernel's operand pattern (accumulator and table value both change every instruction: "
+                            f"kb_peak_measure 7) it is {a / peaks['fp32_gfma_ffma2_two_varying_operands']:.2f}",
                        traffic_note=f"dram read+write bytes per launch: 200.3 MB measured by ncu --set full on a 2^20-candidate launch "
                                     f"(profiles/r02_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches")
         if k == 0 and ms_k > 0:
