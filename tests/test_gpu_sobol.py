@@ -82,3 +82,31 @@ def test_limits(ctx):
         ctx.sobol_fill(1025, 0, 4)
     with pytest.raises(kb.KbError):
         ctx.sobol_fill(4, (1 << 32) - 2, 4)
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_host_fill_streams_in_chunks(golden_dir, pinned):
+    """kb_sobol_fill produces the block in 32 MB chunks through two alternating device buffers, the copy of one chunk
+    behind the generation of the next (pageable destinations additionally through pinned staging).  200 000 points x
+    64 dims x 8 B = 102 MB = four chunks with a ragged last one, scaled to [low, high): every value must equal the
+    oracle's, and a second, smaller call on the same context (buffers reused) as well."""
+    import torch
+    ctx = kb.Context(0)
+    dim, first, n = 64, 12345, 200_000
+    low, high = np.linspace(-3.0, 1.0, dim), np.linspace(2.0, 9.0, dim)
+    if pinned:
+        buf = torch.empty((n, dim), dtype=torch.float64, pin_memory=True)
+        out, ptr = buf.numpy(), buf.data_ptr()
+    else:
+        out = np.empty((n, dim))
+        ptr = out.ctypes.data
+    lo_c, hi_c = np.ascontiguousarray(low), np.ascontiguousarray(high)
+    assert kb.lib().kb_sobol_fill(ctx._h, dim, first, n, lo_c.ctypes.data, hi_c.ctypes.data, ptr) == 0
+    ref = O.sobol(golden_dir, dim, first, n)
+    want = ref * (high - low) + low  # separately rounded multiply and add, like the kernel (and Go)
+    assert np.array_equal(out, want)
+    small = ctx.sobol_fill(dim, 7, 1000)
+    assert np.array_equal(small, O.sobol(golden_dir, dim, 7, 1000))
+    one = ctx.sobol_fill(5, 99, 1)  # what the service asks for: one point
+    assert np.array_equal(one, O.sobol(golden_dir, 5, 99, 1))
+    ctx.close()
