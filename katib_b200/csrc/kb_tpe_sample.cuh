@@ -47,19 +47,29 @@ __device__ __forceinline__ double tpe_sample_one(const KbDim &dm, const Philox &
     const int K = dm.K[0];
     const double *w = dm.w[0], *mu = dm.mu[0], *sg = dm.sigma[0];
     double x = 0.5 * (dm.lo + dm.hi);
-    for (uint32_t attempt = 0; attempt < SAMPLE_MAX_TRIES; attempt++) {
-        // one Philox block per attempt: 32 bits pick the component, 53 bits the radius, 32 bits the angle
-        const uint4 r = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d, attempt + 1u);
-        const double u = ((double)r.x + 0.5) * (1.0 / 4294967296.0);
-        double acc = 0.0;
-        int a = K - 1;
-        for (int j = 0; j < K; j++) { acc += w[j]; if (u < acc) { a = j; break; } }
-        double u1 = u01(r.y, r.z);
-        const double u2 = ((double)r.w + 0.5) * (1.0 / 4294967296.0);
+    // Rejection sampling, two attempts per round: one Box-Muller transform yields two independent normals (R cos, R sin),
+    // each paired with its own component pick.  A lane whose first attempt falls outside [lo, hi) takes the second
+    // without another logarithm, and a warp repeats the round only if some lane lost both -- the attempts are i.i.d.,
+    // so the accepted draw has the distribution of attempt-after-attempt rejection (sampleFromGMM).
+    for (uint32_t round = 0; round < SAMPLE_MAX_TRIES / 2; round++) {
+        const uint4 r = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d, round + 1u);
+        const uint4 r2 = ph((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)d | 0x80000000u, round + 1u);
+        double u1 = u01(r2.x, r2.y);
         u1 = u1 < 1e-300 ? 1e-300 : u1;
-        const double z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);  // Box-Muller
-        const double draw = mu[a] + sg[a] * z;
-        if (dm.lo <= draw && draw < dm.hi) { x = draw; break; }
+        const double rad = sqrt(-2.0 * log(u1));
+        double sn, cs;
+        sincospi(2.0 * (((double)r.z + 0.5) * (1.0 / 4294967296.0)), &sn, &cs);
+        bool done = false;
+#pragma unroll
+        for (int half = 0; half < 2 && !done; half++) {
+            const double u = ((double)(half ? r.y : r.x) + 0.5) * (1.0 / 4294967296.0);
+            double acc = 0.0;
+            int a = K - 1;
+            for (int j = 0; j < K; j++) { acc += w[j]; if (u < acc) { a = j; break; } }
+            const double draw = mu[a] + sg[a] * (rad * (half ? sn : cs));
+            if (dm.lo <= draw && draw < dm.hi) { x = draw; done = true; }
+        }
+        if (done) break;
     }
     if (dm.q > 0.0) x = round(x / dm.q) * dm.q;
     return x;
