@@ -66,7 +66,8 @@ __device__ __forceinline__ double tpe_sample_one(const KbDim &dm, const Philox &
             double acc = 0.0;
             int a = K - 1;
             for (int j = 0; j < K; j++) { acc += w[j]; if (u < acc) { a = j; break; } }
-            const double draw = mu[a] + sg[a] * (rad * (half ? sn : cs));
+            // _rn intrinsics: the same bits in every translation unit, with or without -fmad
+            const double draw = __dadd_rn(mu[a], __dmul_rn(sg[a], __dmul_rn(rad, half ? sn : cs)));
             if (dm.lo <= draw && draw < dm.hi) { x = draw; done = true; }
         }
         if (done) break;

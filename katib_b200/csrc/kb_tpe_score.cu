@@ -164,6 +164,8 @@ tpe_stage_kernel(const KbDim *__restrict__ dims, int D, const double *__restrict
 // straight into the staged column -- the n x D f64 candidate matrix is never materialised.  One CTA = 256 consecutive
 // candidates of ONE parameter (blockIdx.y), so the kind branch is uniform and the column stores coalesce.
 #define SS_THREADS 256
+#define SS_ITEMS 8   // candidates per thread: 64 Mi x 50 one-candidate threads would be 13 M CTAs, and launching them costs
+                     // more than the draws (measured: 135 ms per headline step, unchanged by a sampler half as expensive)
 __global__ void __launch_bounds__(SS_THREADS)
 tpe_sample_stage_kernel(const KbDim *__restrict__ dims, int n, long long chunk_cap, unsigned long long seed, long long first,
                         float2 *__restrict__ stage_cont, float4 *__restrict__ stage_quant, const int *__restrict__ slot_of_dim,
@@ -171,14 +173,16 @@ tpe_sample_stage_kernel(const KbDim *__restrict__ dims, int n, long long chunk_c
     const int d = blockIdx.y;
     const KbDim &dm = dims[d];
     const int slot = slot_of_dim[d];
-    const int i = blockIdx.x * SS_THREADS + threadIdx.x;
     const Philox ph(seed);
     if (dm.kind == KB_CATEGORICAL) {
         unsigned long long best = 0ull;
-        if (i < n) {
+        for (int it = 0; it < SS_ITEMS; it++) {
+            const int i = (blockIdx.x * SS_ITEMS + it) * SS_THREADS + threadIdx.x;
+            if (i >= n) break;
             int c = (int)tpe_sample_one(dm, ph, (unsigned long long)(first + i), d);
             c = c < 0 ? 0 : (c >= dm.n_choices ? dm.n_choices - 1 : c);
-            best = cat_key(dm, c, local_base + i);
+            const unsigned long long key = cat_key(dm, c, local_base + i);
+            best = key > best ? key : best;
         }
         for (int o = 16; o > 0; o >>= 1) {
             const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
@@ -187,10 +191,14 @@ tpe_sample_stage_kernel(const KbDim *__restrict__ dims, int n, long long chunk_c
         if ((threadIdx.x & 31) == 0 && best) atomicMax(&sel[d].cat_best, best);
         return;
     }
-    if (i >= n) return;
-    const double x = tpe_sample_one(dm, ph, (unsigned long long)(first + i), d);
-    if (dm.q > 0.0) stage_quant[(size_t)slot * chunk_cap + i] = stage_value_quant(dm, x);
-    else stage_cont[(size_t)slot * chunk_cap + i] = stage_value_cont(dm, x);
+    const bool quant = dm.q > 0.0;
+    for (int it = 0; it < SS_ITEMS; it++) {
+        const int i = (blockIdx.x * SS_ITEMS + it) * SS_THREADS + threadIdx.x;
+        if (i >= n) break;
+        const double x = tpe_sample_one(dm, ph, (unsigned long long)(first + i), d);
+        if (quant) stage_quant[(size_t)slot * chunk_cap + i] = stage_value_quant(dm, x);
+        else stage_cont[(size_t)slot * chunk_cap + i] = stage_value_cont(dm, x);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1455,7 +1463,7 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
                                                                             sc->d_slot_of_dim, sel, local_base, d_scores);
     } else {
         KbProf pf(ctx, 6, s);
-        tpe_sample_stage_kernel<<<dim3((unsigned)((n + SS_THREADS - 1) / SS_THREADS), (unsigned)D), SS_THREADS, 0, s>>>(
+        tpe_sample_stage_kernel<<<dim3((unsigned)((n + SS_THREADS * SS_ITEMS - 1) / (SS_THREADS * SS_ITEMS)), (unsigned)D), SS_THREADS, 0, s>>>(
             ctx->d_dims, n, ctx->chunk_cap, seed, idx_base, ctx->d_stage_cont, ctx->d_stage_quant, sc->d_slot_of_dim, sel, local_base);
     }
     KB_LAUNCH_CHECK(ctx);
