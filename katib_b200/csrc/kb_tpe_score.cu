@@ -270,11 +270,20 @@ __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_ba
 // Per pair of (candidate, component) evaluations: 2 FADD2 + 2 FFMA2 + 2 MUFU.EX2 + 1 FADD2.
 // ---------------------------------------------------------------------------------------------------------
 #define SC_THREADS 256
+#ifndef SC_R
 #define SC_R 8
+#endif
 #define SC_TILE (SC_THREADS * SC_R)
+#ifndef SC_CHUNK
 #define SC_CHUNK 512   // components per shared-memory stage (2 float4 each: 16 KB)
+#endif
 #define SC_STAGES 2
+#ifndef SC_GROUP
 #define SC_GROUP 32    // components per FP32 partial sum
+#endif
+#ifndef SC_MINB
+#define SC_MINB 3      // CTAs per SM the continuous kernels are compiled for (80 registers)
+#endif
 
 __device__ __forceinline__ void table_stream_issue(const KbDim &dm, int chunk, int nchunk0, float4 *dst, uint64_t *bar) {
     const int side = chunk < nchunk0 ? 0 : 1;
@@ -389,7 +398,7 @@ __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const
 }
 
 template <unsigned SW_MASK>
-__global__ void __launch_bounds__(SC_THREADS, 3)
+__global__ void __launch_bounds__(SC_THREADS, SC_MINB)
 tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                       const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                       KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
