@@ -279,7 +279,10 @@ __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_ba
 #endif
 #define SC_STAGES 2
 #ifndef SC_GROUP
-#define SC_GROUP 32    // components per FP32 partial sum
+// components per FP32 partial sum before it is folded into the (hi, lo) pair: the fold is 48 FADDs per thread, and at 32
+// components it cost 3 % of the kernel.  Measured (2^24 candidates x 20 parameters, worst score error over 2^21 x 20):
+// 32 -> 2240 ms / 5.7e-7, 64 -> 2206 / 6.3e-7, 128 -> 2189 / 8.1e-7, 256 -> 2181 / 1.3e-6, 512 -> 2199 / 2.3e-6.
+#define SC_GROUP 128
 #endif
 #ifndef SC_MINB
 #define SC_MINB 3      // CTAs per SM the continuous kernels are compiled for (80 registers)
@@ -339,10 +342,10 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
 #define SC_SW_DEFAULT 1
 #endif
 template <unsigned SC_SW_MASK>
-__device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, const float2 (&xh)[SC_R / 2],
+__device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int len, const float2 (&xh)[SC_R / 2],
                                            const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
 #pragma unroll 1
-    for (int h = 0; h < SC_GROUP; h += 16) {
+    for (int h = 0; h < len; h += 16) {  // len: a multiple of 16 (tables are padded to KB_TABLE_PAD = 32), at most SC_GROUP
 #pragma unroll
         for (int jj = 0; jj < 16; jj++) {
             const float4 A = tab[2 * (h + jj)], B = tab[2 * (h + jj) + 1];  // two broadcast LDS.128
@@ -443,7 +446,7 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
             float2 a32[SC_R / 2];
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-            cont_group<SW_MASK>(tab + 2 * j0, xh, xl, a32);
+            cont_group<SW_MASK>(tab + 2 * j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
@@ -643,7 +646,7 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
             float2 a32[SC_R / 2];
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-            cont_group<SW_MASK>(tab + 2 * j0, xh, xl, a32);
+            cont_group<SW_MASK>(tab + 2 * j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
