@@ -34,7 +34,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 N_HISTORY = 10_000
 JSON_OUT = sys.stdout  # main() replaces it by a duplicate of the original stdout before anything native can print
 # admission margins of the near-tie table (kb_tpe_score.cu: KB_MARGIN_CONT / KB_MARGIN_QUANT)
-MARGIN_CONT, MARGIN_QUANT = 4e-6, 1.5e-5
+MARGIN_CONT, MARGIN_QUANT = 5e-6, 1.5e-5
 CAT_CHOICES = [2, 3, 4, 6, 8, 12, 16]
 
 
