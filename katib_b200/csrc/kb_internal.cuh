@@ -30,6 +30,10 @@ struct KbDim {
     //   continuous: {-mu_hi x2, c' x2} {-mu_lo*c' x2, k' x2}   c' = sqrt(log2e/2)/sigma_n, k' = (logc-L)*log2e
     //   quantised : {-mu_hi x2, r' x2} {-mu_lo*r' x2, +-w x2}  r' = sqrt(log2e)/(sqrt2 sigma_n); w<0: sigma_min class
     float4 *tab[2];
+    // continuous parameters, what tpe_score_cont_kernel streams: the same four numbers once, {-mu_hi, c', -mu_lo*c', k'}
+    // in ONE float4 per component (FADD2 / FFMA2 take a 32-bit register as a both-halves operand, so nothing needs
+    // duplicating: half the shared-memory loads and TMA bytes of `tab`); Kpad entries
+    float4 *tabc[2];
     // categorical: probabilities and the log-ratio table
     double *cat_p[2];
     double *cat_score;        // log pl[c] - log pg[c]

@@ -394,6 +394,7 @@ __device__ void parzen_body(KbDim &dm, int d, int side, const double *__restrict
         }
         tab[2 * j] = A;
         tab[2 * j + 1] = B;
+        if (!quant) dm.tabc[side][j] = make_float4(A.x, A.z, B.x, B.z);
     }
     // Quantised parameters: split the entries, in order, into the look-up class (grid code != 0: dense weights + run
     // table, see KbDim::qw) and the rest (tabw).  A stable partition by a block scan over per-thread segments, then a
@@ -709,7 +710,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
     for (int d = 0; d < D; d++) {
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
-        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 6 * sizeof(float4)) + KB_LUT_MAX * sizeof(float) +
+        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 7 * sizeof(float4)) + KB_LUT_MAX * sizeof(float) +
                            (KB_LUT_MAX / 2) * sizeof(int4) + (k.q > 0 ? KB_LUT2_FLOATS * sizeof(float) : 0));
     }
     if (bytes > ctx->tabmem_bytes) {
@@ -731,6 +732,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
                 k.tab[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
                 k.tabn[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
                 k.tabw[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
+                k.tabc[side] = (float4 *)p; p += (size_t)Kcap * sizeof(float4);
                 k.mu[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.sigma[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);

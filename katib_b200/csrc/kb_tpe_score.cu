@@ -298,6 +298,16 @@ __device__ __forceinline__ void table_stream_issue(const KbDim &dm, int chunk, i
     tma_bulk_g2s(dst, dm.tab[side] + (size_t)c * SC_CHUNK * 2, bytes, bar);
 }
 
+#define SCC_CHUNK (SC_CHUNK * 2)   // components per stage of the compact table (one float4 each: the same 16 KB)
+__device__ __forceinline__ void table_stream_issue_compact(const KbDim &dm, int chunk, int nchunk0, float4 *dst, uint64_t *bar) {
+    const int side = chunk < nchunk0 ? 0 : 1;
+    const int c = side == 0 ? chunk : chunk - nchunk0;
+    const int cnt = min(SCC_CHUNK, dm.Kpad[side] - c * SCC_CHUNK);
+    const uint32_t bytes = (uint32_t)cnt * (uint32_t)sizeof(float4);
+    mbar_expect_tx(bar, bytes);
+    tma_bulk_g2s(dst, dm.tabc[side] + (size_t)c * SCC_CHUNK, bytes, bar);
+}
+
 // (hi, lo) += a with the rounding error of the add recovered (TwoSum): keeps ~48 bits without touching FP64
 __device__ __forceinline__ void two_sum_acc(float &hi, float &lo, float a) {
     const float s = hi + a;
@@ -342,8 +352,9 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
 #ifndef SC_SW_DEFAULT
 #define SC_SW_DEFAULT 1
 #endif
+// the two-float4 (duplicated) table form: the pruned kernel's windows come out of tabn / tabw
 template <unsigned SC_SW_MASK>
-__device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int len, const float2 (&xh)[SC_R / 2],
+__device__ __forceinline__ void cont_group_dup(const float4 *__restrict__ tab, int len, const float2 (&xh)[SC_R / 2],
                                            const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
 #pragma unroll 1
     for (int h = 0; h < len; h += 16) {  // len: a multiple of 16 (tables are padded to KB_TABLE_PAD = 32), at most SC_GROUP
@@ -401,19 +412,78 @@ __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int l
     }
 }
 
+template <unsigned SC_SW_MASK>
+__device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int len, const float2 (&xh)[SC_R / 2],
+                                           const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
+#pragma unroll 1
+    for (int h = 0; h < len; h += 16) {  // len: a multiple of 16 (tables are padded to KB_TABLE_PAD = 32), at most SC_GROUP
+#pragma unroll
+        for (int jj = 0; jj < 16; jj++) {
+            const float4 T = tab[h + jj];  // one broadcast LDS.128: {-mu_hi, c, -mu_lo c, k}, each a both-halves operand
+            const float2 nmu = make_float2(T.x, T.x), cs = make_float2(T.y, T.y);
+            const float2 ms = make_float2(T.z, T.z), ks = make_float2(T.w, T.w);
+            if ((SC_SW_MASK >> jj) & 1u) {
+                // the four candidate pairs go through the polynomial in lockstep (independent chains back to back)
+                float2 em[SC_R / 2], xm[SC_R / 2], f[SC_R / 2], q[SC_R / 2];
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) {
+                    float2 u = __fadd2_rn(xh[p], nmu);
+                    u = __fadd2_rn(u, xl[p]);
+                    const float2 t = __ffma2_rn(u, cs, ms);
+                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                    em[p] = make_float2(fmaxf(e.x, -127.f), fmaxf(e.y, -127.f));
+                }
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) xm[p] = __fadd2_rn(em[p], make_float2(12582912.f, 12582912.f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) f[p] = __fadd2_rn(xm[p], make_float2(-12582912.f, -12582912.f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) f[p] = __ffma2_rn(f[p], make_float2(-1.f, -1.f), em[p]);
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++)
+                    q[p] = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f[p],
+                                      make_float2(9.675574488937855e-3f, 9.675574488937855e-3f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(5.550701171159744e-2f, 5.550701171159744e-2f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(2.4022118747234344e-1f, 2.4022118747234344e-1f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(1.0000001192092896f, 1.0000001192092896f));
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) {
+                    const float2 v = make_float2(__int_as_float(__float_as_int(q[p].x) + (__float_as_int(xm[p].x) << 23)),
+                                                 __int_as_float(__float_as_int(q[p].y) + (__float_as_int(xm[p].y) << 23)));
+                    a32[p] = __fadd2_rn(a32[p], v);
+                }
+            } else {
+#pragma unroll
+                for (int p = 0; p < SC_R / 2; p++) {
+                    float2 u = __fadd2_rn(xh[p], nmu);
+                    u = __fadd2_rn(u, xl[p]);
+                    const float2 t = __ffma2_rn(u, cs, ms);
+                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
+                }
+            }
+        }
+    }
+}
+
 template <unsigned SW_MASK>
 __global__ void __launch_bounds__(SC_THREADS, SC_MINB)
 tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                       const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                       KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
                       KbRaw cand_raw, double *__restrict__ scores_out) {
-    __shared__ __align__(128) float4 s_tab[SC_STAGES][SC_CHUNK * 2];
+    __shared__ __align__(128) float4 s_tab[SC_STAGES][SCC_CHUNK];
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     const int slot = blockIdx.y;
     const int d = cont_dims[slot];
     const KbDim &dm = dims[d];
     const int tile_base = blockIdx.x * SC_TILE;
-    const int nchunk0 = (dm.Kpad[0] + SC_CHUNK - 1) / SC_CHUNK, nchunk1 = (dm.Kpad[1] + SC_CHUNK - 1) / SC_CHUNK;
+    const int nchunk0 = (dm.Kpad[0] + SCC_CHUNK - 1) / SCC_CHUNK, nchunk1 = (dm.Kpad[1] + SCC_CHUNK - 1) / SCC_CHUNK;
     const int nchunks = nchunk0 + nchunk1;
 
     if (threadIdx.x == 0) {
@@ -422,7 +492,7 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
     }
     __syncthreads();
     if (threadIdx.x == 0)
-        for (int c = 0; c < SC_STAGES && c < nchunks; c++) table_stream_issue(dm, c, nchunk0, s_tab[c], &s_bar[c]);
+        for (int c = 0; c < SC_STAGES && c < nchunks; c++) table_stream_issue_compact(dm, c, nchunk0, s_tab[c], &s_bar[c]);
 
     float2 xh[SC_R / 2], xl[SC_R / 2];  // candidate pairs (r, r+1)
 #pragma unroll
@@ -440,14 +510,14 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
         const int st = c % SC_STAGES;
         const int side = c < nchunk0 ? 0 : 1;
         const int cc = side == 0 ? c : c - nchunk0;
-        const int cnt = min(SC_CHUNK, dm.Kpad[side] - cc * SC_CHUNK);
+        const int cnt = min(SCC_CHUNK, dm.Kpad[side] - cc * SCC_CHUNK);
         mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
         const float4 *tab = s_tab[st];
         for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
             float2 a32[SC_R / 2];
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-            cont_group<SW_MASK>(tab + 2 * j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
+            cont_group<SW_MASK>(tab + j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
@@ -456,7 +526,7 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
         }
         __syncthreads();  // every thread is done with stage st
         if (threadIdx.x == 0 && c + SC_STAGES < nchunks)
-            table_stream_issue(dm, c + SC_STAGES, nchunk0, s_tab[st], &s_bar[st]);
+            table_stream_issue_compact(dm, c + SC_STAGES, nchunk0, s_tab[st], &s_bar[st]);
         if (c == nchunk0 - 1) {
 #pragma unroll
             for (int r = 0; r < SC_R; r++) {
@@ -647,7 +717,7 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
             float2 a32[SC_R / 2];
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
-            cont_group<SW_MASK>(tab + 2 * j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
+            cont_group_dup<SW_MASK>(tab + 2 * j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
 #pragma unroll
             for (int p = 0; p < SC_R / 2; p++) {
                 two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
@@ -724,6 +794,7 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
 #define SQ_MINB 2
 #endif
 #define SQ_TILE (SC_THREADS * SQ_R)
+#define SQ_GROUP 32   // components per FP32 partial sum of tpe_score_quant_kernel; its run cutting works on one warp-wide group
 #define LN2F 0.6931471806f
 #define KINVF 0.8325546112f           // 1/sqrt(log2 e)
 #define QUANT_WIDE_THR 0.2402245f     // (b - a) <= 0.2 in erf units, scaled by sqrt(log2 e)
@@ -824,7 +895,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
             tv_code = 0u;  // the cached table values belong to the other side's table
             __syncthreads();
         }
-        for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
+        for (int j0 = 0; j0 < cnt; j0 += SQ_GROUP) {
             float2 a32[SQ_R / 2];
 #pragma unroll
             for (int p = 0; p < SQ_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
@@ -832,7 +903,7 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
             // sorted by mu) take a branch-free inner loop: one broadcast LDS of the weight and four packed FFMAs per
             // component.  The group is cut into runs of equal grid code with one ballot per run.
             const uint32_t cj = (uint32_t)__float_as_int(tab[2 * (j0 + (int)(threadIdx.x & 31u)) + 1].w);
-            for (int jb = 0, je; jb < SC_GROUP; jb = je) {
+            for (int jb = 0, je; jb < SQ_GROUP; jb = je) {
                 const uint32_t rcode = __shfl_sync(0xffffffffu, cj, jb);
                 const uint32_t eq = __ballot_sync(0xffffffffu, cj == rcode) >> jb;  // bit 0 = component jb itself
                 je = jb + (~eq == 0u ? 32 : __ffs((int)~eq) - 1);
