@@ -101,8 +101,8 @@ int kb_tpe_append_history(kb_ctx *ctx, int64_t n_new, const double *values, cons
 /* KB_OPT_PRUNE_FAR (default 0): continuous parameters only.  A component whose sigma sits on the magic-clip floor and
  * whose mu is more than 7.75 sigma from a candidate contributes less than e^-30 of its own peak to that candidate's
  * mixture value; with the option on such (candidate, component) pairs are not evaluated (candidates are bucketed by
- * value first, so that a thread block meets one window of the mu-sorted table).  Scores change by less than 1e-7
- * relative, winners -- decided in FP64 on the unpruned mixture -- do not.  goptuna evaluates every pair; so does the
+ * value first, so that a thread block meets one window of the mu-sorted table).  Scores change by a few 1e-6
+ * relative (the omitted terms are far smaller; the FP32 summation order differs), winners -- decided in FP64 on the unpruned mixture -- do not.  goptuna evaluates every pair; so does the
  * default. */
 #define KB_OPT_PRUNE_FAR 2
 int kb_tpe_set_option(kb_ctx *ctx, int option, int value);
