@@ -340,17 +340,18 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
 // their 2^e from kb_ex2_fma2 instead, which moves that share of the exponentials onto the otherwise half-idle FMA
 // pipe.  Every (candidate, component) pair is still evaluated.
 // Masks for 0, 1, 2, 3 and 4 of every 16 components.  On paper 3/16 balances the two pipes (XU 13 cycles, FMA 13 cycles
-// per pair-component); measured on B200 at 2^24 candidates x 20 parameters x 10 002 components: 0 -> 2313 ms, 1 -> 2258 ms,
-// 2 -> 2338 ms, 3 -> 2427 ms, 4 -> 2535 ms (ncu at 1/16: XU 89.5 %, FMA pipe 69 %, issue 53 %; the polynomial's dependent
-// chain and the MIO queue stop the two pipes from overlapping further).  1/16 is the default; KB_CONT_SW = 0..4 picks
-// another at run time (measurement only).
+// per pair-component).  Measured on B200 at 2^24 candidates x 20 parameters x 10 002 components, 3 steps: with the
+// two-float4 table and 32-component partial sums 0 -> 2313 ms, 1 -> 2258, 2 -> 2338, 3 -> 2427, 4 -> 2535 (only 1/16
+// paid: the MIO queue, shared by MUFU and LDS, and the fold arithmetic left no room); with the one-float4 table and
+// 128-component partial sums 0 -> 2255, 1 -> 2172, 2 -> 2123, 3 -> 2157, 4 -> 2266.  2/16 is the default: 1.025 of the
+// MUFU.EX2 peak measured by kb_peak_measure.  KB_CONT_SW = 0..4 picks another at run time (measurement only).
 #define SC_SW_MASK_0 0x0000u
 #define SC_SW_MASK_1 0x0100u
 #define SC_SW_MASK_2 0x0404u
 #define SC_SW_MASK_3 0x1084u
 #define SC_SW_MASK_4 0x4444u
 #ifndef SC_SW_DEFAULT
-#define SC_SW_DEFAULT 1
+#define SC_SW_DEFAULT 2
 #endif
 // the two-float4 (duplicated) table form: the pruned kernel's windows come out of tabn / tabw
 template <unsigned SC_SW_MASK>
@@ -1567,7 +1568,7 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
                                                               ctx->d_stage_sorted, ctx->d_perm);
         KB_LAUNCH_CHECK(ctx);
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
-        tpe_score_cont_pruned_kernel<SC_SW_MASK_1><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
+        tpe_score_cont_pruned_kernel<SC_SW_MASK_2><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
                                                                  ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score,
                                                                  ctx->tie_slots, d_cand, d_scores);
         KB_LAUNCH_CHECK(ctx);
@@ -1580,10 +1581,10 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,           \
                                                                 sc->d_tie_score, ctx->tie_slots, d_cand, d_scores)
         if (sw == 0) KB_CONT_LAUNCH(SC_SW_MASK_0);
-        else if (sw == 2) KB_CONT_LAUNCH(SC_SW_MASK_2);
         else if (sw == 4) KB_CONT_LAUNCH(SC_SW_MASK_4);
         else if (sw == 3) KB_CONT_LAUNCH(SC_SW_MASK_3);
-        else KB_CONT_LAUNCH(SC_SW_MASK_1);
+        else if (sw == 1) KB_CONT_LAUNCH(SC_SW_MASK_1);
+        else KB_CONT_LAUNCH(SC_SW_MASK_2);
 #undef KB_CONT_LAUNCH
         KB_LAUNCH_CHECK(ctx);
     }
