@@ -1056,6 +1056,10 @@ tpe_score_quant_kernel(const KbDim *__restrict__ dims, const int *__restrict__ q
 #define SQG_FLUSH 128       // components per FP32 partial sum before it is folded into the (hi, lo) pair (multiple of 4)
 #endif
 #define SQG_OTHER 64        // other-class entries per shared-memory pass
+#ifndef SQG_UNROLL
+#define SQG_UNROLL 2        // LDS.128s of weights per trip of the run loop
+#endif
+constexpr int kSqgUnroll = SQG_UNROLL;
 static_assert(SQG_R == SQ_R, "the grid kernel and tpe_score_quant_kernel must agree on the tile size");
 
 __global__ void __launch_bounds__(SC_THREADS, 3)
@@ -1206,7 +1210,7 @@ tpe_score_quant_grid_kernel(const KbDim *__restrict__ dims, const int *__restric
                 while (j < b) {
                     const int m = min(b - j, SQG_FLUSH - since);
                     const float4 *wp = reinterpret_cast<const float4 *>(w + j);
-#pragma unroll 2
+#pragma unroll kSqgUnroll
                     for (int k = 0; k < m / 4; k++) {
                         const float4 w4 = wp[k];  // one broadcast LDS.128: four weights
                         const float2 wa = make_float2(w4.x, w4.x), wb = make_float2(w4.y, w4.y);
