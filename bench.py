@@ -498,10 +498,10 @@ def main():
         if k == 1 and ms_k > 0:
             a = ce_cont / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
-                       frac=a / peaks["mufu_ex2_gops"], traffic=182.2e6 * launch_rows / float(1 << 20),
-                       note="1 of every 16 exponentials is computed on the FMA pipe (packed FP32 polynomial), so the kernel can "
-                            "read slightly above 15/16 of what MUFU alone allows; every (candidate, component) pair is evaluated",
-                       traffic_note=f"dram read+write bytes per launch: 182.2 MB measured by ncu --set full on a 2^20-candidate launch "
+                       frac=a / peaks["mufu_ex2_gops"], traffic=178.9e6 * launch_rows / float(1 << 20),
+                       note="2 of every 16 exponentials are computed on the FMA pipe (packed FP32 polynomial), so the kernel can "
+                            "read above the MUFU.EX2 peak (the bound is 16/14 of it); every (candidate, component) pair is evaluated",
+                       traffic_note=f"dram read+write bytes per launch: 178.9 MB measured by ncu --set full on a 2^20-candidate launch "
                                     f"(profiles/r02_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches "
                                     "(the traffic is the candidate columns, read once)")
         if k == 2 and ms_k > 0:
