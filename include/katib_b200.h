@@ -83,8 +83,10 @@ int kb_space_set(kb_ctx *ctx, int n_params, const int32_t *kind, const double *l
  * (getObservationPairs over study.GetTrials(); reached from sample.go:48-90): Complete trials only
  * (service.go:134-137), values[n_trials x n_params] row-major internal representation,
  * loss[n_trials] = objective already sign-flipped so that lower is better
- * (toGoptunaDirection, converter.go:31-36).  It uploads the history and builds, on the GPU, the
- * below/above split and both Parzen estimators of every parameter. */
+ * (toGoptunaDirection, converter.go:31-36).  It uploads the history; the below/above split and both
+ * Parzen estimators of every parameter are built on the GPU when an entry point first reads them
+ * (a small kb_tpe_suggest on a history of up to 512 trials builds what it needs inside its own
+ * kernel and never asks for the tables). */
 int kb_tpe_set_history(kb_ctx *ctx, int64_t n_trials, const double *values, const double *loss);
 /* Appends n_new trials to the history already on the device and rebuilds the estimators: the same result as
  * kb_tpe_set_history with the concatenated arrays, but only the new rows cross the boundary.  (The reference
