@@ -31,6 +31,22 @@ def merge_winners(scores, indices, values):
     return out_s, out_i, out_v
 
 
+def merge_status(status_rows):
+    """The status row that travels with the winners through the all-gather (tpe_pick_kernel / tpe_merge_kernel):
+    status_rows[r] = 1 + the highest parameter whose near-tie table overflowed on rank r, 0 = none.  The call's status is
+    the maximum -- an overflow anywhere is an overflow everywhere, so every rank repeats the pass (or fails) together
+    and no rank trusts winners merged from another rank's incomplete table."""
+    return int(max(int(s) for s in status_rows)) if len(status_rows) else 0
+
+
+def suggest_shard(n_ei_candidates, world, rank, shard_min=65536):
+    """Index range of the Philox candidate stream rank draws and scores in kb_tpe_suggest: sharded (shard_range) from
+    shard_min candidates on, otherwise the whole set with no collective."""
+    if world > 1 and n_ei_candidates >= shard_min:
+        return shard_range(n_ei_candidates, world, rank)
+    return 0, n_ei_candidates
+
+
 def population_row_weights(f_all, weights, begin, end):
     """CMA-ES with the population sharded by rows (cma_tell_sharded in kb_cmaes.cu): the recombination weight of each of
     this rank's rows [begin, end).  The ranking is global -- ascending objective value, ties by global row index (a stable

@@ -11,7 +11,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import _oracle as O
-from katib_b200.sharding import merge_winners, shard_range
+from katib_b200.sharding import merge_status, merge_winners, shard_range, suggest_shard
 
 
 def _free_port():
@@ -47,6 +47,14 @@ def _worker(rank, world, port, q):
     dist.all_gather(gathered, local)
     g = torch.stack(gathered).numpy()  # [world, D, 3]
     s, i, v = merge_winners(g[:, :, 0], g[:, :, 1].astype(np.int64), g[:, :, 2])
+    # the status row rides in the same gather: only rank 1 "overflowed" (parameter 1), both ranks must see it
+    st = torch.tensor([0.0 if rank == 0 else 2.0], dtype=torch.float64)
+    sts = [torch.zeros_like(st) for _ in range(world)]
+    dist.all_gather(sts, st)
+    status = merge_status([float(x[0]) for x in sts])
+    statuses = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
+    dist.all_gather(statuses, torch.tensor([float(status)], dtype=torch.float64))
+    assert all(float(x[0]) == 2.0 for x in statuses)  # every rank took the same decision
     if rank == 0:
         q.put((s.tolist(), i.tolist(), v.tolist()))
     dist.barrier()
@@ -59,6 +67,14 @@ def test_shard_range_covers_everything():
         assert spans[0][0] == 0 and spans[-1][1] == n
         assert all(spans[r][1] == spans[r + 1][0] for r in range(w - 1))
         assert max(e - b for b, e in spans) - min(e - b for b, e in spans) <= 1
+
+
+def test_suggest_sharding_rule():
+    assert suggest_shard(24, 8, 3) == (0, 24)                      # small requests: no collective, any rank alone
+    spans = [suggest_shard(1 << 26, 8, r) for r in range(8)]
+    assert spans[0][0] == 0 and spans[-1][1] == 1 << 26 and all(spans[r][1] == spans[r + 1][0] for r in range(7))
+    assert suggest_shard(65536, 2, 1) == (32768, 65536) and suggest_shard(65535, 2, 1) == (0, 65535)
+    assert merge_status([0, 0, 3, 1]) == 3 and merge_status([0, 0]) == 0
 
 
 def test_two_rank_merge_equals_unsharded_oracle():
