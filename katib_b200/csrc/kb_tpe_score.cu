@@ -325,20 +325,12 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
     const float2 xm = __fadd2_rn(em, make_float2(12582912.f, 12582912.f));
     const float2 nf = __fadd2_rn(xm, make_float2(-12582912.f, -12582912.f));
     const float2 f = __ffma2_rn(nf, make_float2(-1.f, -1.f), em);
-#if defined(KB_EX2_DEG) && KB_EX2_DEG == 4   // measurement only: 2.7e-6 relative
-    float2 p = __ffma2_rn(make_float2(9.57401655614376e-3f, 9.57401655614376e-3f), f,
-                          make_float2(5.5918190628290176e-2f, 5.5918190628290176e-2f));
-    p = __ffma2_rn(p, f, make_float2(2.402464896440506e-1f, 2.402464896440506e-1f));
-    p = __ffma2_rn(p, f, make_float2(6.931217312812805e-1f, 6.931217312812805e-1f));
-    p = __ffma2_rn(p, f, make_float2(9.999992847442627e-1f, 9.999992847442627e-1f));
-#else
     float2 p = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f,
                           make_float2(9.675574488937855e-3f, 9.675574488937855e-3f));
     p = __ffma2_rn(p, f, make_float2(5.550701171159744e-2f, 5.550701171159744e-2f));
     p = __ffma2_rn(p, f, make_float2(2.4022118747234344e-1f, 2.4022118747234344e-1f));
     p = __ffma2_rn(p, f, make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
     p = __ffma2_rn(p, f, make_float2(1.0000001192092896f, 1.0000001192092896f));
-#endif
     return make_float2(__int_as_float(__float_as_int(p.x) + (__float_as_int(xm.x) << 23)),
                        __int_as_float(__float_as_int(p.y) + (__float_as_int(xm.y) << 23)));
 }
@@ -389,18 +381,6 @@ __device__ __forceinline__ void cont_group_dup(const float4 *__restrict__ tab, i
                 for (int p = 0; p < SC_R / 2; p++) f[p] = __fadd2_rn(xm[p], make_float2(-12582912.f, -12582912.f));
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++) f[p] = __ffma2_rn(f[p], make_float2(-1.f, -1.f), em[p]);
-#if defined(KB_EX2_DEG) && KB_EX2_DEG == 4   // measurement only: degree 4, 2.7e-6 relative
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++)
-                    q[p] = __ffma2_rn(make_float2(9.57401655614376e-3f, 9.57401655614376e-3f), f[p],
-                                      make_float2(5.5918190628290176e-2f, 5.5918190628290176e-2f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(2.402464896440506e-1f, 2.402464896440506e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931217312812805e-1f, 6.931217312812805e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(9.999992847442627e-1f, 9.999992847442627e-1f));
-#else
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++)
                     q[p] = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f[p],
@@ -413,7 +393,6 @@ __device__ __forceinline__ void cont_group_dup(const float4 *__restrict__ tab, i
                 for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(1.0000001192092896f, 1.0000001192092896f));
-#endif
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++) {
                     const float2 v = make_float2(__int_as_float(__float_as_int(q[p].x) + (__float_as_int(xm[p].x) << 23)),
@@ -461,18 +440,6 @@ __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int l
                 for (int p = 0; p < SC_R / 2; p++) f[p] = __fadd2_rn(xm[p], make_float2(-12582912.f, -12582912.f));
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++) f[p] = __ffma2_rn(f[p], make_float2(-1.f, -1.f), em[p]);
-#if defined(KB_EX2_DEG) && KB_EX2_DEG == 4   // measurement only: degree 4, 2.7e-6 relative
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++)
-                    q[p] = __ffma2_rn(make_float2(9.57401655614376e-3f, 9.57401655614376e-3f), f[p],
-                                      make_float2(5.5918190628290176e-2f, 5.5918190628290176e-2f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(2.402464896440506e-1f, 2.402464896440506e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931217312812805e-1f, 6.931217312812805e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(9.999992847442627e-1f, 9.999992847442627e-1f));
-#else
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++)
                     q[p] = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f[p],
@@ -485,7 +452,6 @@ __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int l
                 for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(1.0000001192092896f, 1.0000001192092896f));
-#endif
 #pragma unroll
                 for (int p = 0; p < SC_R / 2; p++) {
                     const float2 v = make_float2(__int_as_float(__float_as_int(q[p].x) + (__float_as_int(xm[p].x) << 23)),
