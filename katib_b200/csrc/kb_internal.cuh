@@ -154,6 +154,7 @@ struct kb_ctx {
     bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
     bool tpe_prune = false;          // KB_OPT_PRUNE_FAR
     bool lean_attr_set = false;      // dynamic shared-memory limit of the single-kernel suggest raised
+    bool cont_attr_set = false;      // ... of tpe_score_cont_kernel
     bool quant_attr_set = false;     // dynamic shared-memory limit of the quantised score kernels raised
     float2 *d_stage_sorted = nullptr;  // [n_cont][chunk] stage_cont in bucket order (pruned scoring)
     int32_t *d_perm = nullptr;         // [n_cont][chunk] chunk-local index of the candidate at each sorted position

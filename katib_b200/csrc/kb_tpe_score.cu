@@ -269,6 +269,8 @@ __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_ba
 // one issue slot for two candidates) can take them as they come out of one LDS.128 each:
 //   A = {-mu_hi, -mu_hi, c', c'}   B = {-mu_lo*c', -mu_lo*c', k', k'}
 // Per pair of (candidate, component) evaluations: 2 FADD2 + 2 FFMA2 + 2 MUFU.EX2 + 1 FADD2.
+// (This duplicated form feeds the pruned kernel; tpe_score_cont_kernel streams the compact table dm.tabc: one float4
+// {-mu_hi, c', -mu_lo*c', k'} per component, each value a both-halves operand of the packed instructions.)
 // ---------------------------------------------------------------------------------------------------------
 #define SC_THREADS 256
 #ifndef SC_R
@@ -286,8 +288,9 @@ __device__ __forceinline__ void select_publish(const float (&sc)[R], int tile_ba
 #define SC_GROUP 128
 #endif
 #ifndef SC_MINB
-#define SC_MINB 3      // CTAs per SM the continuous kernels are compiled for (80 registers)
+#define SC_MINB 4      // CTAs per SM tpe_score_cont_kernel is compiled for (64 registers, 48 KB of shared memory each)
 #endif
+#define SC_MINB_PRUNED 3   // tpe_score_cont_pruned_kernel keeps its sums in registers (80)
 
 __device__ __forceinline__ void table_stream_issue(const KbDim &dm, int chunk, int nchunk0, float4 *dst, uint64_t *bar) {
     const int side = chunk < nchunk0 ? 0 : 1;
@@ -298,7 +301,9 @@ __device__ __forceinline__ void table_stream_issue(const KbDim &dm, int chunk, i
     tma_bulk_g2s(dst, dm.tab[side] + (size_t)c * SC_CHUNK * 2, bytes, bar);
 }
 
-#define SCC_CHUNK (SC_CHUNK * 2)   // components per stage of the compact table (one float4 each: the same 16 KB)
+#ifndef SCC_CHUNK
+#define SCC_CHUNK 512   // components per stage of the compact table (one float4 each: 8 KB)
+#endif
 __device__ __forceinline__ void table_stream_issue_compact(const KbDim &dm, int chunk, int nchunk0, float4 *dst, uint64_t *bar) {
     const int side = chunk < nchunk0 ? 0 : 1;
     const int c = side == 0 ? chunk : chunk - nchunk0;
@@ -335,150 +340,90 @@ __device__ __forceinline__ float2 kb_ex2_fma2(float2 e) {
                        __int_as_float(__float_as_int(p.y) + (__float_as_int(xm.y) << 23)));
 }
 
-// One group of SC_GROUP (32) components applied to the SC_R candidates of a thread.  The MUFU pipe is the wall of this
-// loop (16 ex2 / clk / SM against 128 FP32 lanes): of every 16 components, those whose bit is set in SC_SW_MASK take
-// their 2^e from kb_ex2_fma2 instead, which moves that share of the exponentials onto the otherwise half-idle FMA
-// pipe.  Every (candidate, component) pair is still evaluated.
-// Masks for 0, 1, 2, 3 and 4 of every 16 components.  On paper 3/16 balances the two pipes (XU 13 cycles, FMA 13 cycles
-// per pair-component).  Measured on B200 at 2^24 candidates x 20 parameters x 10 002 components, 3 steps: with the
-// two-float4 table and 32-component partial sums 0 -> 2313 ms, 1 -> 2258, 2 -> 2338, 3 -> 2427, 4 -> 2535 (only 1/16
-// paid: the MIO queue, shared by MUFU and LDS, and the fold arithmetic left no room); with the one-float4 table and
-// 128-component partial sums 0 -> 2255, 1 -> 2172, 2 -> 2123, 3 -> 2157, 4 -> 2266.  2/16 is the default: 1.025 of the
+// One group of at most SC_GROUP components applied to the SC_R candidates of a thread.  The MUFU pipe is the wall of
+// this loop (16 ex2 / clk / SM against 128 FP32 lanes): a share of the (component, candidate pair) slots take their 2^e
+// from kb_ex2_fma2 instead, which moves that share of the exponentials onto the otherwise half-idle FMA pipe.  Every
+// (candidate, component) pair is still evaluated.
+// The masks give the slots of a block of 16 components x 4 candidate pairs (bit 4 jj + p) for 0, 1, 2, 3 and 4
+// sixteenths.  The slots are spread out -- one pair of one component at a time, the pair rotating -- so that the
+// 9-instruction polynomial chain sits between the MUFU work of the other three pairs, and only one chain's temporaries
+// are live (the kernel fits 64 registers: 4 CTAs per SM).  Measured on B200, 2^24 candidates x 20 parameters x 10 002
+// components, 3 steps (profiles/r02_ncu_tpe_score.md): whole components in lockstep at 3 CTAs/SM 0 -> 2255 ms,
+// 1 -> 2172, 2 -> 2123, 3 -> 2157, 4 -> 2266; spread slots at 3 CTAs/SM 2 -> 2094, 2.5 -> 2112, 3 -> 2157; spread slots
+// at 4 CTAs/SM (the sums in shared memory) 2 -> 2040, 2.5 -> 2067, 3 -> 2144.  2/16 is the default: 1.07 of the
 // MUFU.EX2 peak measured by kb_peak_measure.  KB_CONT_SW = 0..4 picks another at run time (measurement only).
-#define SC_SW_MASK_0 0x0000u
-#define SC_SW_MASK_1 0x0100u
-#define SC_SW_MASK_2 0x0404u
-#define SC_SW_MASK_3 0x1084u
-#define SC_SW_MASK_4 0x4444u
+#define SC_SW_MASK_0 0x0000000000000000ull
+#define SC_SW_MASK_1 0x0008000400020001ull
+#ifndef SC_SW_MASK_2
+#define SC_SW_MASK_2 0x0804020108040201ull
+#endif
+#define SC_SW_MASK_3 0x0421042104210421ull
+#define SC_SW_MASK_4 0x8421842184218421ull
 #ifndef SC_SW_DEFAULT
 #define SC_SW_DEFAULT 2
 #endif
+static_assert(SC_R == 8, "the slot masks are laid out for 4 candidate pairs per thread");
+
+// component jj (of a block of 16) against the four candidate pairs; the table values arrive as both-halves operands
+template <unsigned long long SW_MASK>
+__device__ __forceinline__ void cont_component(int jj, float2 nmu, float2 cs, float2 ms, float2 ks,
+                                               const float2 (&xh)[SC_R / 2], const float2 (&xl)[SC_R / 2],
+                                               float2 (&a32)[SC_R / 2]) {
+#pragma unroll
+    for (int p = 0; p < SC_R / 2; p++) {
+        float2 u = __fadd2_rn(xh[p], nmu);
+        u = __fadd2_rn(u, xl[p]);
+        const float2 t = __ffma2_rn(u, cs, ms);
+        const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
+        if ((SW_MASK >> (jj * (SC_R / 2) + p)) & 1ull) a32[p] = __fadd2_rn(a32[p], kb_ex2_fma2(e));
+        else a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
+    }
+}
+
 // the two-float4 (duplicated) table form: the pruned kernel's windows come out of tabn / tabw
-template <unsigned SC_SW_MASK>
+template <unsigned long long SW_MASK>
 __device__ __forceinline__ void cont_group_dup(const float4 *__restrict__ tab, int len, const float2 (&xh)[SC_R / 2],
-                                           const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
+                                               const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
 #pragma unroll 1
     for (int h = 0; h < len; h += 16) {  // len: a multiple of 16 (tables are padded to KB_TABLE_PAD = 32), at most SC_GROUP
 #pragma unroll
         for (int jj = 0; jj < 16; jj++) {
             const float4 A = tab[2 * (h + jj)], B = tab[2 * (h + jj) + 1];  // two broadcast LDS.128
-            const float2 nmu = make_float2(A.x, A.y), cs = make_float2(A.z, A.w);
-            const float2 ms = make_float2(B.x, B.y), ks = make_float2(B.z, B.w);
-            if ((SC_SW_MASK >> jj) & 1u) {
-                // the four candidate pairs go through the polynomial in lockstep (independent chains back to back)
-                float2 em[SC_R / 2], xm[SC_R / 2], f[SC_R / 2], q[SC_R / 2];
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    float2 u = __fadd2_rn(xh[p], nmu);
-                    u = __fadd2_rn(u, xl[p]);
-                    const float2 t = __ffma2_rn(u, cs, ms);
-                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                    em[p] = make_float2(fmaxf(e.x, -127.f), fmaxf(e.y, -127.f));
-                }
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) xm[p] = __fadd2_rn(em[p], make_float2(12582912.f, 12582912.f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) f[p] = __fadd2_rn(xm[p], make_float2(-12582912.f, -12582912.f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) f[p] = __ffma2_rn(f[p], make_float2(-1.f, -1.f), em[p]);
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++)
-                    q[p] = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f[p],
-                                      make_float2(9.675574488937855e-3f, 9.675574488937855e-3f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(5.550701171159744e-2f, 5.550701171159744e-2f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(2.4022118747234344e-1f, 2.4022118747234344e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(1.0000001192092896f, 1.0000001192092896f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    const float2 v = make_float2(__int_as_float(__float_as_int(q[p].x) + (__float_as_int(xm[p].x) << 23)),
-                                                 __int_as_float(__float_as_int(q[p].y) + (__float_as_int(xm[p].y) << 23)));
-                    a32[p] = __fadd2_rn(a32[p], v);
-                }
-            } else {
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    float2 u = __fadd2_rn(xh[p], nmu);
-                    u = __fadd2_rn(u, xl[p]);
-                    const float2 t = __ffma2_rn(u, cs, ms);
-                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
-                }
-            }
+            cont_component<SW_MASK>(jj, make_float2(A.x, A.y), make_float2(A.z, A.w), make_float2(B.x, B.y),
+                                    make_float2(B.z, B.w), xh, xl, a32);
         }
     }
 }
 
-template <unsigned SC_SW_MASK>
+template <unsigned long long SW_MASK>
 __device__ __forceinline__ void cont_group(const float4 *__restrict__ tab, int len, const float2 (&xh)[SC_R / 2],
                                            const float2 (&xl)[SC_R / 2], float2 (&a32)[SC_R / 2]) {
 #pragma unroll 1
-    for (int h = 0; h < len; h += 16) {  // len: a multiple of 16 (tables are padded to KB_TABLE_PAD = 32), at most SC_GROUP
+    for (int h = 0; h < len; h += 16) {
 #pragma unroll
         for (int jj = 0; jj < 16; jj++) {
             const float4 T = tab[h + jj];  // one broadcast LDS.128: {-mu_hi, c, -mu_lo c, k}, each a both-halves operand
-            const float2 nmu = make_float2(T.x, T.x), cs = make_float2(T.y, T.y);
-            const float2 ms = make_float2(T.z, T.z), ks = make_float2(T.w, T.w);
-            if ((SC_SW_MASK >> jj) & 1u) {
-                // the four candidate pairs go through the polynomial in lockstep (independent chains back to back)
-                float2 em[SC_R / 2], xm[SC_R / 2], f[SC_R / 2], q[SC_R / 2];
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    float2 u = __fadd2_rn(xh[p], nmu);
-                    u = __fadd2_rn(u, xl[p]);
-                    const float2 t = __ffma2_rn(u, cs, ms);
-                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                    em[p] = make_float2(fmaxf(e.x, -127.f), fmaxf(e.y, -127.f));
-                }
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) xm[p] = __fadd2_rn(em[p], make_float2(12582912.f, 12582912.f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) f[p] = __fadd2_rn(xm[p], make_float2(-12582912.f, -12582912.f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) f[p] = __ffma2_rn(f[p], make_float2(-1.f, -1.f), em[p]);
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++)
-                    q[p] = __ffma2_rn(make_float2(1.3280353741720319e-3f, 1.3280353741720319e-3f), f[p],
-                                      make_float2(9.675574488937855e-3f, 9.675574488937855e-3f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(5.550701171159744e-2f, 5.550701171159744e-2f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(2.4022118747234344e-1f, 2.4022118747234344e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(6.931470036506653e-1f, 6.931470036506653e-1f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) q[p] = __ffma2_rn(q[p], f[p], make_float2(1.0000001192092896f, 1.0000001192092896f));
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    const float2 v = make_float2(__int_as_float(__float_as_int(q[p].x) + (__float_as_int(xm[p].x) << 23)),
-                                                 __int_as_float(__float_as_int(q[p].y) + (__float_as_int(xm[p].y) << 23)));
-                    a32[p] = __fadd2_rn(a32[p], v);
-                }
-            } else {
-#pragma unroll
-                for (int p = 0; p < SC_R / 2; p++) {
-                    float2 u = __fadd2_rn(xh[p], nmu);
-                    u = __fadd2_rn(u, xl[p]);
-                    const float2 t = __ffma2_rn(u, cs, ms);
-                    const float2 e = __ffma2_rn(make_float2(-t.x, -t.y), t, ks);
-                    a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
-                }
-            }
+            cont_component<SW_MASK>(jj, make_float2(T.x, T.x), make_float2(T.y, T.y), make_float2(T.z, T.z),
+                                    make_float2(T.w, T.w), xh, xl, a32);
         }
     }
 }
 
-template <unsigned SW_MASK>
+// Shared memory (dynamic, SC_CONT_SMEM bytes = 48 KB): two table stages of SCC_CHUNK one-float4 entries (16 KB), then
+// the per-candidate (hi, lo) sums of the side in progress and those of the finished below side, [2 SC_R][SC_THREADS]
+// floats each (16 KB + 16 KB).  The sums are touched once per SC_GROUP components, so they wait in shared memory and
+// the loop fits 64 registers: 4 CTAs = 32 warps per SM (3 CTAs at 80 registers: 4 % slower, see cont_component).
+#define SC_CONT_SMEM ((size_t)SC_STAGES * SCC_CHUNK * sizeof(float4) + (size_t)4 * SC_R * SC_THREADS * sizeof(float))
+template <unsigned long long SW_MASK>
 __global__ void __launch_bounds__(SC_THREADS, SC_MINB)
 tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                       const float2 *__restrict__ stage, long long chunk_cap, int n, long long idx_base, int D,
                       KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
                       KbRaw cand_raw, double *__restrict__ scores_out) {
-    __shared__ __align__(128) float4 s_tab[SC_STAGES][SCC_CHUNK];
+    extern __shared__ __align__(128) float4 s_dyn[];
+    float4 (*s_tab)[SCC_CHUNK] = reinterpret_cast<float4 (*)[SCC_CHUNK]>(s_dyn);
+    float *s_sum = reinterpret_cast<float *>(s_dyn + SC_STAGES * SCC_CHUNK) + threadIdx.x;  // row 2r: hi, row 2r+1: lo
+    float *s_below = s_sum + 2 * SC_R * SC_THREADS;
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     const int slot = blockIdx.y;
     const int d = cont_dims[slot];
@@ -502,10 +447,8 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
         float2 v = i < n ? stage[(size_t)slot * chunk_cap + i] : make_float2(0.5f, 0.f);
         if (r & 1) { xh[r / 2].y = v.x; xl[r / 2].y = v.y; } else { xh[r / 2].x = v.x; xl[r / 2].x = v.y; }
     }
-    float Shi[SC_R], Slo[SC_R];
-    double logS0[SC_R];
 #pragma unroll
-    for (int r = 0; r < SC_R; r++) { Shi[r] = 0.f; Slo[r] = 0.f; }
+    for (int k = 0; k < 2 * SC_R; k++) s_sum[k * SC_THREADS] = 0.f;  // each thread reads and writes its own column only
 
     for (int c = 0; c < nchunks; c++) {
         const int st = c % SC_STAGES;
@@ -520,26 +463,28 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
             for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
             cont_group<SW_MASK>(tab + j0, min(SC_GROUP, cnt - j0), xh, xl, a32);
 #pragma unroll
-            for (int p = 0; p < SC_R / 2; p++) {
-                two_sum_acc(Shi[2 * p], Slo[2 * p], a32[p].x);
-                two_sum_acc(Shi[2 * p + 1], Slo[2 * p + 1], a32[p].y);
+            for (int p = 0; p < SC_R / 2; p++) {  // fold the FP32 partial sums into the (hi, lo) pairs
+                float *q = s_sum + 4 * p * SC_THREADS;
+                float h0 = q[0], l0 = q[SC_THREADS], h1 = q[2 * SC_THREADS], l1 = q[3 * SC_THREADS];
+                two_sum_acc(h0, l0, a32[p].x);
+                two_sum_acc(h1, l1, a32[p].y);
+                q[0] = h0; q[SC_THREADS] = l0; q[2 * SC_THREADS] = h1; q[3 * SC_THREADS] = l1;
             }
         }
         __syncthreads();  // every thread is done with stage st
         if (threadIdx.x == 0 && c + SC_STAGES < nchunks)
             table_stream_issue_compact(dm, c + SC_STAGES, nchunk0, s_tab[st], &s_bar[st]);
-        if (c == nchunk0 - 1) {
+        if (c == nchunk0 - 1) {  // the below side is complete: park its sums, start the above side from zero
 #pragma unroll
-            for (int r = 0; r < SC_R; r++) {
-                logS0[r] = log((double)Shi[r] + (double)Slo[r]) + dm.L[0];
-                Shi[r] = 0.f; Slo[r] = 0.f;
-            }
+            for (int k = 0; k < 2 * SC_R; k++) { s_below[k * SC_THREADS] = s_sum[k * SC_THREADS]; s_sum[k * SC_THREADS] = 0.f; }
         }
     }
     float sc[SC_R];
 #pragma unroll
     for (int r = 0; r < SC_R; r++) {
-        double s64 = logS0[r] - (log((double)Shi[r] + (double)Slo[r]) + dm.L[1]);
+        const double below = log((double)s_below[2 * r * SC_THREADS] + (double)s_below[(2 * r + 1) * SC_THREADS]) + dm.L[0];
+        const double above = log((double)s_sum[2 * r * SC_THREADS] + (double)s_sum[(2 * r + 1) * SC_THREADS]) + dm.L[1];
+        const double s64 = below - above;
         sc[r] = (float)s64;
         int i = tile_base + r * SC_THREADS + threadIdx.x;
         if (scores_out && i < n) scores_out[(size_t)i * D + d] = s64;
@@ -627,8 +572,8 @@ tpe_bucket_scatter_kernel(const float2 *__restrict__ stage, long long chunk_cap,
 
 struct PruneSeg { const float4 *p; int cnt; int c0; int nch; };  // table segment: entries (multiple of 32), first chunk, chunks
 
-template <unsigned SW_MASK>
-__global__ void __launch_bounds__(SC_THREADS, 3)
+template <unsigned long long SW_MASK>
+__global__ void __launch_bounds__(SC_THREADS, SC_MINB_PRUNED)
 tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
                              const float2 *__restrict__ sorted, const int32_t *__restrict__ perm, long long chunk_cap, int n,
                              long long idx_base, int D, KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
@@ -1581,8 +1526,14 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
         KbProf pf(ctx, 1, s);
         static const int sw = [] { const char *e = getenv("KB_CONT_SW"); return e ? atoi(e) : SC_SW_DEFAULT; }();
+        if (!ctx->cont_attr_set) {  // once per context: 48 KB of dynamic shared memory + the barriers is over the default
+#define KB_CONT_ATTR(MASK) KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_cont_kernel<MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SC_CONT_SMEM))
+            KB_CONT_ATTR(SC_SW_MASK_0); KB_CONT_ATTR(SC_SW_MASK_1); KB_CONT_ATTR(SC_SW_MASK_2); KB_CONT_ATTR(SC_SW_MASK_3); KB_CONT_ATTR(SC_SW_MASK_4);
+#undef KB_CONT_ATTR
+            ctx->cont_attr_set = true;
+        }
 #define KB_CONT_LAUNCH(MASK)                                                                                              \
-        tpe_score_cont_kernel<MASK><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont,           \
+        tpe_score_cont_kernel<MASK><<<grid, SC_THREADS, SC_CONT_SMEM, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_cont,           \
                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie,           \
                                                                 sc->d_tie_score, ctx->tie_slots, d_cand, d_scores)
         if (sw == 0) KB_CONT_LAUNCH(SC_SW_MASK_0);
