@@ -323,6 +323,11 @@ def main():
     clk = clocks.stop() if rank == 0 else None
     launches = ctx.launch_count() - launches0
     value = n_total * args.steps / (ms * 1e-3)
+    own, wide = ctx.tpe_local_stats()  # warm-up + timed steps of this rank
+    local_blocks = {"own_origin": own, "hi_lo_form": wide,
+                    "note": "thread blocks of tpe_score_cont_local_kernel (KB_OPT_LOCAL_ORIGIN, default on): candidates bucketed by "
+                            "value, x - mu measured from the block's own origin (one instruction less per pair); blocks whose "
+                            "candidates span more than 1/128 of the range keep the (hi, lo) form"}
 
     # ---- end to end: host buffers through the public C-ABI call
     e2e = None
@@ -552,6 +557,7 @@ def main():
                                       "oracle/tpe.c single thread (goptuna's path is sequential: service.go:77-88)"},
            "suggest_whole_set": suggest, "merged_duplicates": merged, "pruned": pruned, "latency": latency,
            "winners_vs_oracle": winners_vs_oracle, "score_error_max": score_error, "secondary": secondary,
+           "local_origin_blocks": local_blocks,
            "winners_index_head": [int(i) for i in res[0][:6]], "wall_s_timed_region": wall}
     print(json.dumps(out), file=JSON_OUT, flush=True)
     shutdown()

@@ -107,6 +107,15 @@ int kb_tpe_append_history(kb_ctx *ctx, int64_t n_new, const double *values, cons
  * relative (the omitted terms are far smaller; the FP32 summation order differs), winners -- decided in FP64 on the unpruned mixture -- do not.  goptuna evaluates every pair; so does the
  * default. */
 #define KB_OPT_PRUNE_FAR 2
+/* KB_OPT_LOCAL_ORIGIN (default 1): continuous parameters, how x - mu is formed in the FP32 scoring kernel; every
+ * (candidate, component) pair is evaluated either way and the winners are decided in FP64 as always.
+ *   0  candidates stay in their order; x and mu are (hi, lo) FP32 pairs on the parameter's whole range.
+ *   1  chunks of at least 32 768 candidates are first bucketed by value (as under KB_OPT_PRUNE_FAR), so that the 2048
+ *      candidates of a thread block lie close together; the block then measures candidates and components from its
+ *      own origin, where one FP32 number resolves 2^-32 of the range, and needs one instruction less per pair.
+ *      Blocks whose candidates span more than 1/128 of the range keep the (hi, lo) form.  Smaller chunks as under 0.
+ *   2  as 1 for every chunk size (tests). */
+#define KB_OPT_LOCAL_ORIGIN 3
 int kb_tpe_set_option(kb_ctx *ctx, int option, int value);
 
 /* Estimator of parameter `param`, side 0 = below (l), 1 = above (g): K entries sorted by mu.
@@ -278,6 +287,10 @@ int kb_profile_read(kb_ctx *ctx, int kernel_class, double *ms_total, int64_t *la
  * operations per (candidate, component): minutes at the headline size.  The admission margins of the near-tie
  * table must stay above these numbers. */
 int kb_tpe_score_error_device(kb_ctx *ctx, int64_t n_cand, const double *cand_device, double *out_max_err);
+/* KB_OPT_LOCAL_ORIGIN: thread blocks of tpe_score_cont_local_kernel run on this context so far that used their own
+ * origin (out_blocks[0]) and that kept the (hi, lo) form because their candidates were spread too widely
+ * (out_blocks[1]). */
+int kb_tpe_local_stats(kb_ctx *ctx, uint64_t *out_blocks);
 /* number of kernels this library has launched on this ctx since creation */
 int64_t kb_launch_count(const kb_ctx *ctx);
 

@@ -71,6 +71,7 @@ def lib():
         "kb_tpe_score_select_device": ([vp, i64, vp, i64, vp, vp, vp, vp], i32),
         "kb_tpe_suggest": ([vp, i64, u64, vp], i32),
         "kb_tpe_score_error_device": ([vp, i64, vp, vp], i32),
+        "kb_tpe_local_stats": ([vp, vp], i32),
         "kb_tpe_sample_candidates": ([vp, i64, u64, vp, vp, vp], i32),
         "kb_sobol_fill": ([vp, i32, u64, i64, vp, vp, vp], i32),
         "kb_sobol_fill_device": ([vp, i32, u64, i64, vp, vp, vp, vp], i32),
@@ -297,6 +298,12 @@ class Context:
         out = np.zeros(self.D)
         self._ck(lib().kb_tpe_score_error_device(self._h, n, dev_ptr, _ptr(out)))
         return out
+
+    def tpe_local_stats(self):
+        """(blocks that used their own origin, blocks that kept the (hi, lo) form) of the KB_OPT_LOCAL_ORIGIN kernel"""
+        out = np.zeros(2, dtype=np.uint64)
+        self._ck(lib().kb_tpe_local_stats(self._h, _ptr(out)))
+        return int(out[0]), int(out[1])
 
     def tpe_suggest(self, n_ei_candidates, seed):
         out = np.zeros(self.D)

@@ -34,6 +34,12 @@ struct KbDim {
     // in ONE float4 per component (FADD2 / FFMA2 take a 32-bit register as a both-halves operand, so nothing needs
     // duplicating: half the shared-memory loads and TMA bytes of `tab`); Kpad entries
     float4 *tabc[2];
+    // ... and what tpe_score_cont_local_kernel streams: {normalised mu in FP64 (low word, high word), c', k'} in the
+    // narrow / wide partition of tabn / tabw below (narrow entries first, padded to KB_TABLE_PAD, then the wide ones);
+    // every thread block turns a stage of it into FP32 entries about its own origin (see that kernel).  c0 = the c' all
+    // narrow components share.
+    float4 *tabs[2];
+    float c0[2];
     // categorical: probabilities and the log-ratio table
     double *cat_p[2];
     double *cat_score;        // log pl[c] - log pg[c]
@@ -153,8 +159,10 @@ struct kb_ctx {
     std::vector<char> h_dims_sent;   // the descriptor table as last uploaded (d_dims is rewritten only when it differs)
     bool tpe_merge = false;          // KB_OPT_MERGE_DUPLICATES
     bool tpe_prune = false;          // KB_OPT_PRUNE_FAR
+    int tpe_local = 1;               // KB_OPT_LOCAL_ORIGIN: 0 never, 1 when a chunk has >= KB_LOCAL_MIN_ROWS rows, 2 always
     bool lean_attr_set = false;      // dynamic shared-memory limit of the single-kernel suggest raised
     bool cont_attr_set = false;      // ... of tpe_score_cont_kernel
+    bool local_attr_set = false;     // ... of tpe_score_cont_local_kernel
     bool quant_attr_set = false;     // dynamic shared-memory limit of the quantised score kernels raised
     float2 *d_stage_sorted = nullptr;  // [n_cont][chunk] stage_cont in bucket order (pruned scoring)
     int32_t *d_perm = nullptr;         // [n_cont][chunk] chunk-local index of the candidate at each sorted position

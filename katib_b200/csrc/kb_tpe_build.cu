@@ -554,16 +554,24 @@ __device__ void parzen_body(KbDim &dm, int d, int side, const double *__restrict
         const int Kn = s_int[nt - 1], Kw = K - Kn;
         int bn = s_int[tid] - c, bw = b0 - bn;
         float4 *tn = dm.tabn[side], *tw = dm.tabw[side];
+        // ... and the same partition once more as the source of tpe_score_cont_local_kernel's per-block tables,
+        // {normalised mu in FP64 (low word, high word), c', k'}: narrow entries first, wide ones from the padded Kn on
+        const int Knp = (Kn + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD, Kwp = (Kw + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
+        float4 *sn = dm.tabs[side], *sw = dm.tabs[side] + Knp;
         for (int j = b0; j < b1; j++) {
-            if (sg[j] == minsigma2) { tn[2 * bn] = tab[2 * j]; tn[2 * bn + 1] = tab[2 * j + 1]; bn++; }
-            else { tw[2 * bw] = tab[2 * j]; tw[2 * bw + 1] = tab[2 * j + 1]; bw++; }
+            const double mun = (mu[j] - low) * inv_range;
+            const float4 S = make_float4(__int_as_float(__double2loint(mun)), __int_as_float(__double2hiint(mun)), tab[2 * j].z, tab[2 * j + 1].z);
+            if (sg[j] == minsigma2) { tn[2 * bn] = tab[2 * j]; tn[2 * bn + 1] = tab[2 * j + 1]; sn[bn] = S; bn++; }
+            else { tw[2 * bw] = tab[2 * j]; tw[2 * bw + 1] = tab[2 * j + 1]; sw[bw] = S; bw++; }
         }
         const float4 Z = make_float4(0.f, 0.f, 0.f, 0.f), NI = make_float4(0.f, 0.f, -INFINITY, -INFINITY);
-        for (int j = Kn + tid; j < (Kn + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { tn[2 * j] = Z; tn[2 * j + 1] = NI; }
-        for (int j = Kw + tid; j < (Kw + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD; j += nt) { tw[2 * j] = Z; tw[2 * j + 1] = NI; }
+        const float4 SP = make_float4(0.f, 0.f, 0.f, -INFINITY);  // mu = 0, c' = 0, k' = -inf: contributes 2^-inf
+        for (int j = Kn + tid; j < Knp; j += nt) { tn[2 * j] = Z; tn[2 * j + 1] = NI; sn[j] = SP; }
+        for (int j = Kw + tid; j < Kwp; j += nt) { tw[2 * j] = Z; tw[2 * j + 1] = NI; sw[j] = SP; }
         if (tid == 0) {
             dm.Kn[side] = Kn; dm.Kw[side] = Kw;
             dm.prune_w[side] = (float)(7.75 * minsigma2 * inv_range * (1.0 + 1e-6));
+            dm.c0[side] = (float)(sqrt(0.5 * LOG2E) * (high - low) / minsigma2);  // c' of every narrow component
         }
     }
 }
@@ -710,7 +718,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
     for (int d = 0; d < D; d++) {
         const KbDim &k = ctx->h_dims[(size_t)d];
         if (k.kind == KB_CATEGORICAL) bytes += (size_t)pad_to(k.n_choices, 32) * (3 * sizeof(double) + sizeof(double));
-        else bytes += 2 * ((size_t)Kcap * (4 * sizeof(double) + 7 * sizeof(float4)) + KB_LUT_MAX * sizeof(float) +
+        else bytes += 2 * (((size_t)Kcap * (4 * sizeof(double) + 8 * sizeof(float4)) + 2 * KB_TABLE_PAD * sizeof(float4)) + KB_LUT_MAX * sizeof(float) +
                            (KB_LUT_MAX / 2) * sizeof(int4) + (k.q > 0 ? KB_LUT2_FLOATS * sizeof(float) : 0));
     }
     if (bytes > ctx->tabmem_bytes) {
@@ -733,6 +741,7 @@ static int tpe_load_history(kb_ctx *ctx, const char *who, int64_t keep64, int64_
                 k.tabn[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
                 k.tabw[side] = (float4 *)p; p += 2 * (size_t)Kcap * sizeof(float4);
                 k.tabc[side] = (float4 *)p; p += (size_t)Kcap * sizeof(float4);
+                k.tabs[side] = (float4 *)p; p += ((size_t)Kcap + 2 * KB_TABLE_PAD) * sizeof(float4);  // two padded parts
                 k.mu[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.sigma[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
                 k.w[side] = (double *)p; p += (size_t)Kcap * sizeof(double);
@@ -920,6 +929,11 @@ extern "C" int kb_tpe_set_option(kb_ctx *ctx, int option, int value) {
     }
     if (option == KB_OPT_PRUNE_FAR) {  // both table forms are always built: nothing to redo
         ctx->tpe_prune = value != 0;
+        return KB_OK;
+    }
+    if (option == KB_OPT_LOCAL_ORIGIN) {
+        if (value < 0 || value > 2) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_option: KB_OPT_LOCAL_ORIGIN takes 0, 1 or 2");
+        ctx->tpe_local = value;
         return KB_OK;
     }
     return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_set_option: unknown option %d", option);

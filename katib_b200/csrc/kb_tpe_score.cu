@@ -493,6 +493,43 @@ tpe_score_cont_kernel(const KbDim *__restrict__ dims, const int *__restrict__ co
                                                   KB_MARGIN_CONT, cand_raw);
 }
 
+// select_publish for candidates in bucket order: the scores belong to the chunk-local indices orig[] (= perm[] of the
+// sorted position, -1 past the end); block maximum and near-tie admission as in select_publish.
+__device__ __forceinline__ void select_publish_perm(const float (&sc)[SC_R], const int (&orig)[SC_R], long long idx_base,
+                                                    int d, int D, const KbDim &dm, KbSelect *sel, KbTie *tie,
+                                                    float *tie_score, unsigned int slots, KbRaw cand_raw) {
+    __shared__ float s_wmax[SC_THREADS / 32];
+    __shared__ float s_thr;
+    float best = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < SC_R; r++)
+        if (orig[r] >= 0) best = fmaxf(best, sc[r]);
+    for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if ((threadIdx.x & 31) == 0) s_wmax[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float b = s_wmax[0];
+        for (int w = 1; w < SC_THREADS / 32; w++) b = fmaxf(b, s_wmax[w]);
+        const unsigned int mine = kb_f32_orderable(b);
+        const unsigned int old = atomicMax(&sel[d].gmax_bits, mine);
+        const float g = kb_f32_from_orderable(old > mine ? old : mine);
+        const float thr = g - KB_MARGIN_CONT * fmaxf(1.0f, fabsf(g));
+        s_thr = b >= thr ? thr : INFINITY;
+    }
+    __syncthreads();
+    const float thr = s_thr;
+    if (thr == INFINITY) return;
+    KbTie *ttab = tie + (size_t)dm.numeric_slot * slots;
+    float *tsc = tie_score + (size_t)dm.numeric_slot * slots;
+#pragma unroll
+    for (int r = 0; r < SC_R; r++) {
+        if (orig[r] >= 0 && sc[r] >= thr) {
+            const unsigned long long key = (unsigned long long)__double_as_longlong(kb_raw_value(cand_raw, dm, orig[r], idx_base + orig[r], D, d));
+            tie_insert(ttab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + orig[r]), sc[r]);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // KB_OPT_PRUNE_FAR, continuous parameters: candidates are bucketed by value (256 buckets over the normalised range, a
 // counting sort per chunk that keeps the chunk-local index), so that the 2048 candidates of a thread block span about
@@ -582,8 +619,6 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
     __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
     __shared__ PruneSeg s_seg[4];
     __shared__ float s_lo[SC_THREADS / 32], s_hi[SC_THREADS / 32];
-    __shared__ float s_wmax[SC_THREADS / 32];
-    __shared__ float s_thr;
     const int slot = blockIdx.y;
     const int d = cont_dims[slot];
     const KbDim &dm = dims[d];
@@ -680,47 +715,235 @@ tpe_score_cont_pruned_kernel(const KbDim *__restrict__ dims, const int *__restri
             }
         }
     }
-    // scores belong to the candidates' chunk-local indices perm[]; the block maximum / near-tie admission is that of
-    // select_publish, with the index indirection
     float sc[SC_R];
     int orig[SC_R];
-    float best = -INFINITY;
 #pragma unroll
     for (int r = 0; r < SC_R; r++) {
         const double s64 = logS0[r] - (log((double)Shi[r] + (double)Slo[r]) + dm.L[1]);
         sc[r] = (float)s64;
         const int i = tile_base + r * SC_THREADS + threadIdx.x;
         orig[r] = i < n ? perm[(size_t)slot * chunk_cap + i] : -1;
-        if (orig[r] >= 0) {
-            if (scores_out) scores_out[(size_t)orig[r] * D + d] = s64;
-            best = fmaxf(best, sc[r]);
+        if (orig[r] >= 0 && scores_out) scores_out[(size_t)orig[r] * D + d] = s64;
+    }
+    if (sel) select_publish_perm(sc, orig, idx_base, d, D, dm, sel, tie, tie_score, slots, cand_raw);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// KB_OPT_LOCAL_ORIGIN, continuous parameters: the same sums as tpe_score_cont_kernel with fewer packed instructions per
+// (candidate pair, component): 3 instead of 5 on the FMA pipe for nearly every component.
+//
+// The (hi, lo) pair of a candidate exists because one FP32 number resolves only 2^-24 of the parameter's range and
+// x - mu is needed to about 2^-31 of it.  Here the candidates arrive in bucket order (tpe_bucket_* above), so the 2048
+// of a thread block lie within a bucket or two, and the block measures everything from its own origin B (the middle of
+// its candidates) in units of the narrow components' sigma: xs = (x - B) c0, |xs| < 0.3, one FP32 number good to 2^-26.
+// The table cannot be prepared for every B, so a stage arrives as {mu (FP64), c', k'} (dm.tabs, TMA) and the block
+// rewrites it in place -- a few FP64 operations per component per block, against 2048 evaluations of it:
+//   narrow component (sigma on the magic-clip floor, c' = c0: all but a handful):  {-(mu-B) c0, k'}
+//        t = xs + (-M)                e = -t t + k'       FADD2, FFMA2 (+ the FADD2 that accumulates 2^e)
+//   wide component (the prior, sparse regions):                                    {-(mu-B) c0, c'/c0, k'}
+//        t = (xs + (-M)) (c'/c0)      e = -t t + k'       FADD2, FMUL2, FFMA2
+// M is rounded to FP32 where it is large, i.e. for components far from every candidate of the block, whose terms are
+// negligible; near ones (|t| < 6) have |M| < 7 and an absolute error below 2^-25 * 8 in t.  With the FMA pipe
+// relieved, more of the exponentials fit on it (SW_N / SW_W slots of 64).
+// A block whose candidates span more than KB_LOCAL_SPAN (thin tails) keeps B = 0 and the (hi, lo) form of
+// tpe_score_cont_kernel: still every pair, just not faster.
+// ---------------------------------------------------------------------------------------------------------
+#define KB_LOCAL_SPAN 0.0078125f   // 2 buckets of 1/256: what a block in a well-filled region spans at most
+#define KB_LOCAL_MIN_ROWS 32768    // KB_OPT_LOCAL_ORIGIN = 1: chunks below this keep their order (sorting would not pay)
+#ifndef SC_SW_LOCAL_DEFAULT
+#define SC_SW_LOCAL_DEFAULT 16     // of 64 slots, narrow components (measured: 12 -> 1882 ms, 16 -> 1812, 18 -> 1828, 20 -> 1884, 24 -> 2043)
+#endif
+#define SC_SW_LOCAL_WIDE 12        // of 64 slots, wide components
+
+template <unsigned long long SW_MASK>
+__device__ __forceinline__ void cont_group_own_narrow(const float4 *__restrict__ tab, int len, const float2 (&xs)[SC_R / 2],
+                                                      float2 (&a32)[SC_R / 2]) {
+#pragma unroll 1
+    for (int h = 0; h < len; h += 16) {
+#pragma unroll
+        for (int jj = 0; jj < 16; jj++) {
+            const float2 T = *reinterpret_cast<const float2 *>(tab + h + jj);  // {-M, k'}
+            const float2 nm = make_float2(T.x, T.x), ks = make_float2(T.y, T.y);
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) {
+                const float2 tt = __fadd2_rn(xs[p], nm);
+                const float2 e = __ffma2_rn(make_float2(-tt.x, -tt.y), tt, ks);
+                if ((SW_MASK >> (jj * (SC_R / 2) + p)) & 1ull) a32[p] = __fadd2_rn(a32[p], kb_ex2_fma2(e));
+                else a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
+            }
         }
     }
-    if (!sel) return;
-    for (int o = 16; o > 0; o >>= 1) best = fmaxf(best, __shfl_xor_sync(0xffffffffu, best, o));
-    if ((threadIdx.x & 31) == 0) s_wmax[threadIdx.x >> 5] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float b = s_wmax[0];
-        for (int w = 1; w < SC_THREADS / 32; w++) b = fmaxf(b, s_wmax[w]);
-        const unsigned int mine = kb_f32_orderable(b);
-        const unsigned int old = atomicMax(&sel[d].gmax_bits, mine);
-        const float g = kb_f32_from_orderable(old > mine ? old : mine);
-        const float thr = g - KB_MARGIN_CONT * fmaxf(1.0f, fabsf(g));
-        s_thr = b >= thr ? thr : INFINITY;
+}
+
+template <unsigned long long SW_MASK>
+__device__ __forceinline__ void cont_group_own_wide(const float4 *__restrict__ tab, int len, const float2 (&xs)[SC_R / 2],
+                                                    float2 (&a32)[SC_R / 2]) {
+#pragma unroll 1
+    for (int h = 0; h < len; h += 16) {
+#pragma unroll
+        for (int jj = 0; jj < 16; jj++) {
+            const float4 T = tab[h + jj];  // {-M, c'/c0, k', -}
+            const float2 nm = make_float2(T.x, T.x), rho = make_float2(T.y, T.y), ks = make_float2(T.z, T.z);
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) {
+                const float2 tt = __fmul2_rn(__fadd2_rn(xs[p], nm), rho);
+                const float2 e = __ffma2_rn(make_float2(-tt.x, -tt.y), tt, ks);
+                if ((SW_MASK >> (jj * (SC_R / 2) + p)) & 1ull) a32[p] = __fadd2_rn(a32[p], kb_ex2_fma2(e));
+                else a32[p] = __fadd2_rn(a32[p], make_float2(kb_ex2(e.x), kb_ex2(e.y)));
+            }
+        }
     }
+}
+
+// n of the 64 (component, pair) slots of a 16-component block on the FMA pipe: component floor(16 k / n), pair k mod 4
+__host__ __device__ constexpr unsigned long long kb_sw_slots(int n) {
+    unsigned long long m = 0;
+    for (int k = 0; k < n; k++) m |= 1ull << (((k * 16) / n) * (SC_R / 2) + (k % (SC_R / 2)));
+    return m;
+}
+static_assert(kb_sw_slots(8) == SC_SW_MASK_2 && kb_sw_slots(16) == SC_SW_MASK_4 && kb_sw_slots(4) == SC_SW_MASK_1, "slot layout");
+
+template <unsigned long long SW_N>
+__global__ void __launch_bounds__(SC_THREADS, SC_MINB)
+tpe_score_cont_local_kernel(const KbDim *__restrict__ dims, const int *__restrict__ cont_dims,
+                            const float2 *__restrict__ sorted, const int32_t *__restrict__ perm, long long chunk_cap, int n,
+                            long long idx_base, int D, KbSelect *sel, KbTie *tie, float *tie_score, unsigned int slots,
+                            KbRaw cand_raw, double *__restrict__ scores_out, unsigned long long *__restrict__ stats) {
+    extern __shared__ __align__(128) float4 s_dyn[];
+    float4 (*s_tab)[SCC_CHUNK] = reinterpret_cast<float4 (*)[SCC_CHUNK]>(s_dyn);
+    float *s_sum = reinterpret_cast<float *>(s_dyn + SC_STAGES * SCC_CHUNK) + threadIdx.x;
+    float *s_below = s_sum + 2 * SC_R * SC_THREADS;
+    __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
+    __shared__ float s_lo[SC_THREADS / 32], s_hi[SC_THREADS / 32];
+    __shared__ PruneSeg s_seg[4];  // below narrow, below wide, above narrow, above wide
+    const int slot = blockIdx.y;
+    const int d = cont_dims[slot];
+    const KbDim &dm = dims[d];
+    const int tile_base = blockIdx.x * SC_TILE;
+    const float2 *mine = sorted + (size_t)slot * chunk_cap + tile_base + threadIdx.x;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < SC_STAGES; s++) mbar_init(&s_bar[s], 1);
+        mbar_fence_init();
+        int c0 = 0;
+        for (int side = 0; side < 2; side++) {
+            const int Knp = (dm.Kn[side] + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
+            const int Kwp = (dm.Kw[side] + KB_TABLE_PAD - 1) / KB_TABLE_PAD * KB_TABLE_PAD;
+            PruneSeg a, b;
+            a.p = dm.tabs[side]; a.cnt = Knp; a.nch = (Knp + SCC_CHUNK - 1) / SCC_CHUNK; a.c0 = c0; c0 += a.nch;
+            b.p = dm.tabs[side] + Knp; b.cnt = Kwp; b.nch = (Kwp + SCC_CHUNK - 1) / SCC_CHUNK; b.c0 = c0; c0 += b.nch;
+            s_seg[2 * side] = a; s_seg[2 * side + 1] = b;
+        }
+    }
+    // the range of the block's candidates
+    float lo = INFINITY, hi = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < SC_R; r++)
+        if (tile_base + r * SC_THREADS + threadIdx.x < n) { const float v = mine[r * SC_THREADS].x; lo = fminf(lo, v); hi = fmaxf(hi, v); }
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
     __syncthreads();
-    const float thr = s_thr;
-    if (thr == INFINITY) return;
-    KbTie *ttab = tie + (size_t)dm.numeric_slot * slots;
-    float *tsc = tie_score + (size_t)dm.numeric_slot * slots;
+    const int nchunks = s_seg[3].c0 + s_seg[3].nch;
+    const int side1_first = s_seg[2].c0;
+    auto seg_of = [&](int c) { int s = 0; while (s < 3 && c >= s_seg[s].c0 + s_seg[s].nch) s++; return s; };
+    auto issue = [&](int c, int st) {  // thread 0 only
+        const int s = seg_of(c);
+        const int cc = c - s_seg[s].c0;
+        const uint32_t bytes = (uint32_t)min(SCC_CHUNK, s_seg[s].cnt - cc * SCC_CHUNK) * (uint32_t)sizeof(float4);
+        mbar_expect_tx(&s_bar[st], bytes);
+        tma_bulk_g2s(s_tab[st], s_seg[s].p + (size_t)cc * SCC_CHUNK, bytes, &s_bar[st]);
+    };
+    if (threadIdx.x == 0)
+        for (int c = 0; c < SC_STAGES && c < nchunks; c++) issue(c, c);
+    float bl = s_lo[0], bh = s_hi[0];
+#pragma unroll
+    for (int w = 1; w < SC_THREADS / 32; w++) { bl = fminf(bl, s_lo[w]); bh = fmaxf(bh, s_hi[w]); }
+    const bool own = bh - bl <= KB_LOCAL_SPAN;   // block-uniform
+    const double B = own ? (double)(0.5f * (bl + bh)) : 0.0;
+    if (stats && threadIdx.x == 0) atomicAdd(&stats[own ? 0 : 1], 1ull);
+
+    // own origin: xh = xs = (x - B) c0 of the side in progress (one rounding, from FP64), xl unused;
+    // otherwise (hi, lo) of x as staged.  Rows past the end sit on the origin.
+    float2 xh[SC_R / 2], xl[SC_R / 2];
+    auto load_candidates = [&](int side) {
+        const double c0 = (double)dm.c0[side];
+#pragma unroll
+        for (int r = 0; r < SC_R; r++) {
+            float2 v = make_float2(0.5f, 0.f);
+            const bool valid = tile_base + r * SC_THREADS + threadIdx.x < n;
+            if (valid) v = mine[r * SC_THREADS];
+            if (own) v = make_float2(valid ? (float)((((double)v.x - B) + (double)v.y) * c0) : 0.f, 0.f);
+            if (r & 1) { xh[r / 2].y = v.x; xl[r / 2].y = v.y; } else { xh[r / 2].x = v.x; xl[r / 2].x = v.y; }
+        }
+    };
+    load_candidates(0);
+#pragma unroll
+    for (int k = 0; k < 2 * SC_R; k++) s_sum[k * SC_THREADS] = 0.f;
+
+    for (int c = 0; c < nchunks; c++) {
+        const int st = c % SC_STAGES;
+        const int s = seg_of(c);
+        const int cnt = min(SCC_CHUNK, s_seg[s].cnt - (c - s_seg[s].c0) * SCC_CHUNK);
+        const bool seg_narrow = (s & 1) == 0;
+        mbar_wait(&s_bar[st], (uint32_t)((c / SC_STAGES) & 1));
+        {   // the stage, rewritten about B
+            const double c0 = (double)dm.c0[s >> 1];
+            for (int e = threadIdx.x; e < cnt; e += SC_THREADS) {
+                const float4 S = s_tab[st][e];
+                const double m = __hiloint2double(__float_as_int(S.y), __float_as_int(S.x)) - B;
+                float4 T;
+                if (!own) { const float mh = (float)m; T = make_float4(-mh, S.z, (float)(-(m - (double)mh) * (double)S.z), S.w); }
+                else if (seg_narrow) T = make_float4((float)(-m * (double)S.z), S.w, 0.f, 0.f);
+                else T = make_float4((float)(-m * c0), (float)((double)S.z / c0), S.w, 0.f);
+                s_tab[st][e] = T;
+            }
+        }
+        __syncthreads();
+        const float4 *tab = s_tab[st];
+        for (int j0 = 0; j0 < cnt; j0 += SC_GROUP) {
+            float2 a32[SC_R / 2];
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) a32[p] = make_float2(0.f, 0.f);
+            const int len = min(SC_GROUP, cnt - j0);
+            if (!own) cont_group<SC_SW_MASK_2>(tab + j0, len, xh, xl, a32);
+            else if (seg_narrow) cont_group_own_narrow<SW_N>(tab + j0, len, xh, a32);
+            else cont_group_own_wide<kb_sw_slots(SC_SW_LOCAL_WIDE)>(tab + j0, len, xh, a32);
+#pragma unroll
+            for (int p = 0; p < SC_R / 2; p++) {
+                float *q = s_sum + 4 * p * SC_THREADS;
+                float h0 = q[0], l0 = q[SC_THREADS], h1 = q[2 * SC_THREADS], l1 = q[3 * SC_THREADS];
+                two_sum_acc(h0, l0, a32[p].x);
+                two_sum_acc(h1, l1, a32[p].y);
+                q[0] = h0; q[SC_THREADS] = l0; q[2 * SC_THREADS] = h1; q[3 * SC_THREADS] = l1;
+            }
+        }
+        __syncthreads();  // every thread is done with stage st
+        if (threadIdx.x == 0 && c + SC_STAGES < nchunks) {
+            // the stage was written through the generic proxy; the bulk copy writes it through the async proxy
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue(c + SC_STAGES, st);
+        }
+        if (c == side1_first - 1) {  // the below side is complete: park its sums, rescale the candidates for the above side
+#pragma unroll
+            for (int k = 0; k < 2 * SC_R; k++) { s_below[k * SC_THREADS] = s_sum[k * SC_THREADS]; s_sum[k * SC_THREADS] = 0.f; }
+            if (own) load_candidates(1);
+        }
+    }
+    float sc[SC_R];
+    int orig[SC_R];
 #pragma unroll
     for (int r = 0; r < SC_R; r++) {
-        if (orig[r] >= 0 && sc[r] >= thr) {
-            const unsigned long long key = (unsigned long long)__double_as_longlong(kb_raw_value(cand_raw, dm, orig[r], idx_base + orig[r], D, d));
-            tie_insert(ttab, tsc, slots, &sel[d], key, (unsigned long long)(idx_base + orig[r]), sc[r]);
-        }
+        const double below = log((double)s_below[2 * r * SC_THREADS] + (double)s_below[(2 * r + 1) * SC_THREADS]) + dm.L[0];
+        const double above = log((double)s_sum[2 * r * SC_THREADS] + (double)s_sum[(2 * r + 1) * SC_THREADS]) + dm.L[1];
+        const double s64 = below - above;
+        sc[r] = (float)s64;
+        const int i = tile_base + r * SC_THREADS + threadIdx.x;
+        orig[r] = i < n ? perm[(size_t)slot * chunk_cap + i] : -1;
+        if (orig[r] >= 0 && scores_out) scores_out[(size_t)orig[r] * D + d] = s64;
     }
+    if (sel) select_publish_perm(sc, orig, idx_base, d, D, dm, sel, tie, tie_score, slots, cand_raw);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1486,7 +1709,7 @@ static int tpe_ensure_scratch(kb_ctx *ctx, int64_t rows, int64_t n_cand, bool ne
 // d_cand_in == nullptr: the chunk's candidates are global indices [idx_base, idx_base + n) of the Philox stream `seed`,
 // drawn straight into the staged columns (kb_tpe_suggest)
 static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long long idx_base, long long local_base, bool select,
-                            double *d_scores, cudaStream_t s, unsigned long long seed = 0) {
+                            double *d_scores, cudaStream_t s, unsigned long long seed = 0, bool as_selection = false) {
     kb_ctx *sc = ctx;
     const int D = ctx->D;
     KbSelect *sel = select ? ctx->d_sel : nullptr;
@@ -1502,11 +1725,22 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
             ctx->d_dims, n, ctx->chunk_cap, seed, idx_base, ctx->d_stage_cont, ctx->d_stage_quant, sc->d_slot_of_dim, sel, local_base);
     }
     KB_LAUNCH_CHECK(ctx);
-    if (ctx->n_cont > 0 && ctx->tpe_prune) {
+    // KB_CONT_LOCAL=0 / 2 overrides KB_OPT_LOCAL_ORIGIN for every context of the process (measurement only)
+    static const int local_env = [] { const char *e = getenv("KB_CONT_LOCAL"); return e ? atoi(e) : -1; }();
+    const int local_opt = local_env >= 0 ? local_env : ctx->tpe_local;
+    // bucketing uses atomics, so the composition of a block -- and with it the last bits of an FP32 score -- changes from
+    // run to run (the winners, decided in FP64, do not): kb_tpe_scores keeps the ordered kernel unless the option says 2
+    const bool ordered_scores = d_scores != nullptr && !as_selection;
+    const bool local = !ctx->tpe_prune && (local_opt == 2 || (local_opt == 1 && n >= KB_LOCAL_MIN_ROWS && !ordered_scores));
+    if (ctx->n_cont > 0 && (ctx->tpe_prune || local)) {
         const size_t per = (size_t)ctx->chunk_cap * (size_t)ctx->n_cont;
         if (!ctx->d_stage_sorted) KB_CUDA(ctx, cudaMalloc(&ctx->d_stage_sorted, sizeof(float2) * per));
         if (!ctx->d_perm) KB_CUDA(ctx, cudaMalloc(&ctx->d_perm, sizeof(int32_t) * per));
-        if (!ctx->d_bucket) KB_CUDA(ctx, cudaMalloc(&ctx->d_bucket, sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont));
+        if (!ctx->d_bucket) {  // bucket counters of the counting sort, then the two block counters of kb_tpe_local_stats
+            const size_t b = sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont;
+            KB_CUDA(ctx, cudaMalloc(&ctx->d_bucket, b + 2 * sizeof(unsigned long long)));
+            KB_CUDA(ctx, cudaMemsetAsync((char *)ctx->d_bucket + b, 0, 2 * sizeof(unsigned long long), s));
+        }
         KbProf pf(ctx, 1, s);
         KB_CUDA(ctx, cudaMemsetAsync(ctx->d_bucket, 0, sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont, s));
         dim3 bgrid((unsigned)((n + BK_THREADS * BK_ITEMS - 1) / (BK_THREADS * BK_ITEMS)), (unsigned)ctx->n_cont);
@@ -1518,9 +1752,32 @@ static int tpe_launch_chunk(kb_ctx *ctx, const double *d_cand_in, int n, long lo
                                                               ctx->d_stage_sorted, ctx->d_perm);
         KB_LAUNCH_CHECK(ctx);
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
-        tpe_score_cont_pruned_kernel<SC_SW_MASK_2><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
-                                                                 ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score,
-                                                                 ctx->tie_slots, d_cand, d_scores);
+        if (ctx->tpe_prune) {
+            tpe_score_cont_pruned_kernel<SC_SW_MASK_2><<<grid, SC_THREADS, 0, s>>>(ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm,
+                                                                     ctx->chunk_cap, n, idx_base, D, sel, ctx->d_tie, sc->d_tie_score,
+                                                                     ctx->tie_slots, d_cand, d_scores);
+        } else {
+            // slots of 64 on the FMA pipe in blocks that use their own origin (KB_CONT_SW_LOCAL: measurement only)
+            static const int swl = [] { const char *e = getenv("KB_CONT_SW_LOCAL"); return e ? atoi(e) : SC_SW_LOCAL_DEFAULT; }();
+            unsigned long long *stats = (unsigned long long *)((char *)ctx->d_bucket + sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont);
+            if (!ctx->local_attr_set) {
+#define KB_LOCAL_ATTR(N) KB_CUDA(ctx, cudaFuncSetAttribute(tpe_score_cont_local_kernel<kb_sw_slots(N)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SC_CONT_SMEM))
+                KB_LOCAL_ATTR(12); KB_LOCAL_ATTR(16); KB_LOCAL_ATTR(18); KB_LOCAL_ATTR(20); KB_LOCAL_ATTR(22); KB_LOCAL_ATTR(24);
+#undef KB_LOCAL_ATTR
+                ctx->local_attr_set = true;
+            }
+#define KB_LOCAL_LAUNCH(N)                                                                                               \
+            tpe_score_cont_local_kernel<kb_sw_slots(N)><<<grid, SC_THREADS, SC_CONT_SMEM, s>>>(                          \
+                ctx->d_dims, ctx->d_cont_dims, ctx->d_stage_sorted, ctx->d_perm, ctx->chunk_cap, n, idx_base, D, sel,    \
+                ctx->d_tie, sc->d_tie_score, ctx->tie_slots, d_cand, d_scores, stats)
+            if (swl <= 12) KB_LOCAL_LAUNCH(12);
+            else if (swl <= 16) KB_LOCAL_LAUNCH(16);
+            else if (swl <= 18) KB_LOCAL_LAUNCH(18);
+            else if (swl <= 20) KB_LOCAL_LAUNCH(20);
+            else if (swl <= 22) KB_LOCAL_LAUNCH(22);
+            else KB_LOCAL_LAUNCH(24);
+#undef KB_LOCAL_LAUNCH
+        }
         KB_LAUNCH_CHECK(ctx);
     } else if (ctx->n_cont > 0) {
         dim3 grid((unsigned)((n + SC_TILE - 1) / SC_TILE), (unsigned)ctx->n_cont);
@@ -1851,6 +2108,19 @@ tpe_score_error_kernel(const KbDim *__restrict__ dims, const int *__restrict__ n
     }
 }
 
+extern "C" int kb_tpe_local_stats(kb_ctx *ctx, uint64_t *out_blocks) {
+    if (!ctx) return KB_ERR_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KbDeviceGuard g(ctx->device);
+    if (!out_blocks) return kb_fail(ctx, KB_ERR_INVALID, "kb_tpe_local_stats: out_blocks is NULL");
+    out_blocks[0] = out_blocks[1] = 0;
+    if (!ctx->d_bucket) return KB_OK;  // the bucketed path has not run on this context
+    const char *stats = (const char *)ctx->d_bucket + sizeof(int32_t) * KB_PRUNE_BUCKETS * (size_t)ctx->n_cont;
+    KB_CUDA(ctx, cudaMemcpyAsync(out_blocks, stats, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    KB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return KB_OK;
+}
+
 extern "C" int kb_tpe_score_error_device(kb_ctx *ctx, int64_t n_cand, const double *cand_device, double *out_max_err) {
     if (!ctx) return KB_ERR_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -1869,7 +2139,7 @@ extern "C" int kb_tpe_score_error_device(kb_ctx *ctx, int64_t n_cand, const doub
     cudaMemsetAsync(d_err, 0, sizeof(unsigned long long) * (size_t)D, s);
     for (int64_t off = 0; off < n_cand && !rc; off += rows) {
         const int n = (int)std::min<int64_t>(rows, n_cand - off);
-        rc = tpe_launch_chunk(ctx, cand_device + (size_t)off * D, n, off, off, false, ctx->d_scores_chunk, s);
+        rc = tpe_launch_chunk(ctx, cand_device + (size_t)off * D, n, off, off, false, ctx->d_scores_chunk, s, 0, true);  // the kernels selection uses
         if (rc) break;
         tpe_score_error_kernel<<<148 * 8, RS_THREADS, 0, s>>>(ctx->d_dims, ctx->d_numeric_dims, ctx->n_numeric, D, n,
                                                               cand_device + (size_t)off * D, ctx->d_scores_chunk, d_err);
