@@ -326,8 +326,8 @@ def main():
     own, wide = ctx.tpe_local_stats()  # warm-up + timed steps of this rank
     local_blocks = {"own_origin": own, "hi_lo_form": wide,
                     "note": "thread blocks of tpe_score_cont_local_kernel (KB_OPT_LOCAL_ORIGIN, default on): candidates bucketed by "
-                            "value, x - mu measured from the block's own origin (one instruction less per pair); blocks whose "
-                            "candidates span more than 1/128 of the range keep the (hi, lo) form"}
+                            "value, x - mu measured from the block's own origin (3 instead of 5 packed instructions per pair-component); "
+                            "blocks whose candidates span more than 1/128 of the range keep the (hi, lo) form"}
 
     # ---- end to end: host buffers through the public C-ABI call
     e2e = None
@@ -493,7 +493,7 @@ def main():
     launch_rows = min(n_local, 1 << int(os.environ.get("KB_CHUNK_LOG2", "22")))  # candidates per kernel launch (staged chunk)
     ce_cont = float(n_local) * n_cont * (K_l + K_g) * args.steps
     ce_quant = float(n_local) * n_quant * (K_l + K_g) * args.steps
-    names = ["tpe_stage_kernel", "tpe_score_cont_kernel", "tpe_score_quant_grid_kernel (+ tpe_score_quant_kernel for off-grid tiles: none here)",
+    names = ["tpe_stage_kernel", "tpe_score_cont_local_kernel (+ tpe_bucket_count / _scan / _scatter, timed with it)", "tpe_score_quant_grid_kernel (+ tpe_score_quant_kernel for off-grid tiles: none here)",
              "tpe_rescore+pick"]
     tot = sum(p[0] for p in prof.values()) or 1.0
     kern = []
@@ -503,12 +503,15 @@ def main():
         if k == 1 and ms_k > 0:
             a = ce_cont / (ms_k * 1e-3) / 1e9
             ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
-                       frac=a / peaks["mufu_ex2_gops"], traffic=178.9e6 * launch_rows / float(1 << 20),
-                       note="2 of every 16 exponentials are computed on the FMA pipe (packed FP32 polynomial), so the kernel can "
-                            "read above the MUFU.EX2 peak (the bound is 16/14 of it); every (candidate, component) pair is evaluated",
-                       traffic_note=f"dram read+write bytes per launch: 178.9 MB measured by ncu --set full on a 2^20-candidate launch "
+                       frac=a / peaks["mufu_ex2_gops"], traffic=273.9e6 * launch_rows / float(1 << 20),
+                       note="16 of every 64 exponentials (12 of 64 for the few wide components) are computed on the FMA pipe "
+                            "(packed FP32 polynomial), so the kernel can read above the MUFU.EX2 peak (the bound is 64/48 of "
+                            "it); every (candidate, component) pair is evaluated.  The time includes the three bucketing "
+                            "kernels that put the candidates in value order for it",
+                       traffic_note=f"dram read+write bytes per launch: 273.9 MB measured by ncu --set full on a 2^20-candidate launch "
                                     f"(profiles/r02_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches "
-                                    "(the traffic is the candidate columns, read once)")
+                                    "(the candidate columns in bucket order, read for the block's range and once per side, "
+                                    "and the index permutation)")
         if k == 2 and ms_k > 0:
             a = ce_quant / (ms_k * 1e-3) / 1e9
             ent.update(bound="fp32", unit="G bin-integral evals/s (1 FP32 FMA lane-op each as executed: look-up class)", achieved=a,

@@ -110,11 +110,14 @@ int kb_tpe_append_history(kb_ctx *ctx, int64_t n_new, const double *values, cons
 /* KB_OPT_LOCAL_ORIGIN (default 1): continuous parameters, how x - mu is formed in the FP32 scoring kernel; every
  * (candidate, component) pair is evaluated either way and the winners are decided in FP64 as always.
  *   0  candidates stay in their order; x and mu are (hi, lo) FP32 pairs on the parameter's whole range.
- *   1  chunks of at least 32 768 candidates are first bucketed by value (as under KB_OPT_PRUNE_FAR), so that the 2048
- *      candidates of a thread block lie close together; the block then measures candidates and components from its
- *      own origin, where one FP32 number resolves 2^-32 of the range, and needs one instruction less per pair.
- *      Blocks whose candidates span more than 1/128 of the range keep the (hi, lo) form.  Smaller chunks as under 0.
- *   2  as 1 for every chunk size (tests). */
+ *   1  with a history of at least 2048 trials (below that the bucketing costs more than it saves), chunks of at
+ *      least 32 768 candidates of a selection pass are first bucketed by value (as under KB_OPT_PRUNE_FAR), so that
+ *      the 2048 candidates of a thread block lie close together; the block then measures candidates and components
+ *      from its own origin in units of the narrow components' sigma, where one FP32 number is enough, and needs 3
+ *      instead of 5 packed instructions per (candidate pair, component) for nearly every component.
+ *      Blocks whose candidates span more than 1/128 of the range keep the (hi, lo) form.  Everything else as under 0,
+ *      kb_tpe_scores included: bucketing uses atomics, so the last bits of an FP32 score would change from run to run.
+ *   2  as 1 for every chunk size, history length and entry point (tests). */
 #define KB_OPT_LOCAL_ORIGIN 3
 int kb_tpe_set_option(kb_ctx *ctx, int option, int value);
 

@@ -95,6 +95,13 @@ def main():
     v_full = full.tpe_suggest(200_000, seed=77)
     v_sh = sharded.tpe_suggest(200_000, seed=77)
     check("case1 suggest: sharded == single", np.array_equal(v_sh, v_full), f"{v_sh} vs {v_full}")
+    # the same with the bucketed kernel (KB_OPT_LOCAL_ORIGIN = 2: whatever the history length) on the sharded side only
+    sharded.tpe_set_option(3, 2)
+    v_loc = sharded.tpe_suggest(200_000, seed=77)
+    idx_l = sharded.tpe_score_select(mine, index_offset=off)[0]
+    sharded.tpe_set_option(3, 1)
+    check("case1 suggest, bucketed kernel: sharded == single", np.array_equal(v_loc, v_full), f"{v_loc} vs {v_full}")
+    check("case1 host, bucketed kernel: sharded == oracle", list(idx_l) == best, f"{list(idx_l)} vs {best}")
     if rank == 0:  # below the threshold there is no collective: one rank may call alone
         check("case1 suggest small: lone rank", np.array_equal(sharded.tpe_suggest(24, seed=5), full.tpe_suggest(24, seed=5)))
 

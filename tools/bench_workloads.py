@@ -170,7 +170,7 @@ def tpe20(args, device=0, emit=True):
         "e2e": {"value": nc / e2e_s, "unit": "candidates/s", "h2d_bytes_per_step": nc * D * 8, "d2h_bytes_per_step": D * 24},
         "gpu_launches": sum(p[1] for p in prof.values()),
         "roofline": {"bound": "sfu", "achieved": a, "peak": mufu, "unit": "G component-evals/s (1 MUFU.EX2 each)", "frac": a / mufu,
-                     "traffic": None, "kernel": "tpe_score_cont_kernel",
+                     "traffic": None, "kernel": "tpe_score_cont_local_kernel",
                      "kernels": [{"class": k, "ms_total": prof[k][0], "launches": prof[k][1]} for k in range(4)],
                      "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel, this GPU, this run (of measured)"},
         "cpu_baseline": {"value": m / cpu_s, "unit": "candidates/s", "cores": 1, "kind": "port",
