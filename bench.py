@@ -502,11 +502,18 @@ def main():
         ent = {"name": names[k], "ms_total": ms_k, "launches": n_k, "share_of_kernel_time": ms_k / tot}
         if k == 1 and ms_k > 0:
             a = ce_cont / (ms_k * 1e-3) / 1e9
-            ent.update(bound="sfu", unit="G component-evals/s (1 MUFU.EX2 each)", achieved=a, peak=peaks["mufu_ex2_gops"],
-                       frac=a / peaks["mufu_ex2_gops"], traffic=273.9e6 * launch_rows / float(1 << 20),
-                       note="16 of every 64 exponentials (12 of 64 for the few wide components) are computed on the FMA pipe "
-                            "(packed FP32 polynomial), so the kernel can read above the MUFU.EX2 peak (the bound is 64/48 of "
-                            "it); every (candidate, component) pair is evaluated.  The time includes the three bucketing "
+            # the kernel sends 48 of every 64 exponentials through MUFU.EX2 (56 of 64 in the ordered kernel) and computes
+            # the rest on the FMA pipe: its SFU ceiling is the measured MUFU.EX2 peak times 64/48 (64/56)
+            on_fma = 16 if own + wide > 0 else 8
+            sfu_ceiling = peaks["mufu_ex2_gops"] * 64.0 / (64 - on_fma)
+            ent.update(bound="sfu", unit="G component-evals/s (one exponential each)", achieved=a, peak=sfu_ceiling,
+                       frac=a / sfu_ceiling, mufu_ex2_peak=peaks["mufu_ex2_gops"], frac_of_mufu_ex2_peak=a / peaks["mufu_ex2_gops"],
+                       traffic=273.9e6 * launch_rows / float(1 << 20),
+                       note=f"{on_fma} of every 64 exponentials (12 of 64 for the few wide components) are computed on the FMA pipe "
+                            f"(packed FP32 polynomial), the other {64 - on_fma} by MUFU.EX2: `peak` is the measured MUFU.EX2 peak "
+                            f"(`mufu_ex2_peak`) times 64/{64 - on_fma}, the rate at which the XU pipe would be saturated; "
+                            "`frac_of_mufu_ex2_peak` is the same rate against the MUFU.EX2 peak alone (the figure of earlier "
+                            "rounds).  Every (candidate, component) pair is evaluated.  The time includes the three bucketing "
                             "kernels that put the candidates in value order for it",
                        traffic_note=f"dram read+write bytes per launch: 273.9 MB measured by ncu --set full on a 2^20-candidate launch "
                                     f"(profiles/r02_ncu_tpe_score.md), scaled to this run's {launch_rows}-candidate launches "
@@ -534,8 +541,10 @@ def main():
     dom = max((e for e in kern if "frac" in e), key=lambda e: e["ms_total"])
     roofline = {"bound": dom["bound"], "achieved": dom["achieved"], "peak": dom["peak"], "unit": dom["unit"],
                 "frac": dom["frac"], "traffic": dom.get("traffic"), "kernel": dom["name"],
-                "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel on this GPU in this run (of measured); "
-                               "MEASURED_PEAKS.json has HBM and bf16 only",
+                "peak_source": "kb_peak_measure MUFU.EX2 micro-kernel on this GPU in this run (of measured), scaled by the share of "
+                               "exponentials the kernel sends to MUFU.EX2 (see the kernel's note); MEASURED_PEAKS.json has HBM "
+                               "and bf16 only",
+                "frac_of_mufu_ex2_peak": dom.get("frac_of_mufu_ex2_peak"),
                 "kernels": kern, "measured_peaks": peaks}
     # BASELINE.json's metric names two figures: candidates/s (above) and the GetSuggestions p50 latency, which is quoted on
     # configs[0] (3 parameters, 100 trials, 24 candidates) -- measured here on rank 0's GPU, a few hundred calls
