@@ -392,18 +392,13 @@ static Status Validate(const ExperimentMsg *e) {
     return Status();
 }
 
-static const Param *find_param(const std::vector<Param> &space, const std::string &name) {
-    for (const Param &p : space) if (p.name == name) return &p;
-    return nullptr;
-}
-
 // toGoptunaTrials + toGoptunaParams + toGoptunaState + getFinalMetric (converter.go:186-343)
 static bool ConvertTrials(const std::vector<TrialMsg> &in, const std::string &metric, const std::vector<Param> &space,
                           std::vector<ConvertedTrial> &out, std::string &err) {
     out.clear();
     out.reserve(in.size());
     std::map<std::string, size_t> by_name;  // position in `out`
-    std::map<std::string, const Param *> param_of;  // first entry of a name wins, as in find_param
+    std::map<std::string, const Param *> param_of;  // first entry of a name wins
     for (const Param &p : space) param_of.emplace(p.name, &p);
     for (const TrialMsg &kt : in) {
         ConvertedTrial t; t.name = kt.name; t.digest = kt.digest;
